@@ -1,0 +1,179 @@
+/*
+ * llb200 - B200-native (sm_100a) kernels for lit-llama-ja's quantized-inference hot path.
+ *
+ * Drop-in boundary: a C-ABI shared library (plain pointers and sizes, no torch types).
+ * Every pointer is a DEVICE pointer unless it says "host".  Every call enqueues work on
+ * `stream` (a cudaStream_t passed as void*) and returns immediately; nothing synchronises.
+ * Return value: LL_OK or a negative LL_ERR_* code; ll_last_error() then holds a message
+ * (thread-local).  Nothing throws across this boundary.
+ *
+ * "ref:" citations are into /root/reference (if001/lit-llama-ja); each entry point names
+ * the reference interface it replaces.  The reference has no native code on this path: its
+ * FFI-equivalent is the Triton launcher + the PyTorch fallback inside
+ * lit_llama/quantization.py, bitsandbytes for llm.int8, and ATen ops in lit_llama/model.py.
+ */
+#ifndef LLB200_H
+#define LLB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LL_ABI_VERSION 1
+
+#define LL_OK 0
+#define LL_ERR_ARG (-1)         /* bad shape / dtype / null pointer */
+#define LL_ERR_CUDA (-2)        /* a CUDA runtime/driver call failed */
+#define LL_ERR_UNSUPPORTED (-3) /* valid request this build has no kernel for */
+
+/* element types of activation / parameter buffers */
+#define LL_F32 0
+#define LL_BF16 1
+#define LL_F16 2
+
+typedef void* ll_stream; /* cudaStream_t */
+
+#if defined(__GNUC__)
+#define LL_API __attribute__((visibility("default")))
+#else
+#define LL_API
+#endif
+
+LL_API const char* ll_last_error(void);
+LL_API int ll_abi_version(void);
+/* number of SMs of the current device (host query; <0 on error) */
+LL_API int ll_sm_count(void);
+
+/* ---------------------------------------------------------------------------------------
+ * GPTQ column-block storage (ref: lit_llama/quantization.py:339-372).
+ *   qw      uint8, logical [N][K/epb], MEMORY [K/epb][N] (N fastest) - the reference's
+ *           column-major buffer, used in place.  epb = 8/bits; entry nr of a byte sits at
+ *           bit nr*bits (bits=4: even k = low nibble).
+ *   scales, zeros  [N][G] row-major, G = ceil(K/tile); tile_cols = -1 means tile = K.
+ * ------------------------------------------------------------------------------------- */
+
+/* ref: ColBlockQuantizedLinear.pack_weight, quantization.py:374-388.  Bit-exact: per group,
+ * in the weight dtype, `/= scale` then `+= zero`, clamp [0, 2^bits-1], TRUNCATE to uint8. */
+LL_API int ll_pack_weight(const void* weight /*[N][K]*/, int weight_dtype, const void* scales, const void* zeros,
+                   int param_dtype, uint8_t* qw, int N, int K, int bits, int tile_cols, ll_stream stream);
+
+/* ref: ColBlockQuantizedLinear.get_weight, quantization.py:390-409.  Bit-exact: code as float,
+ * `-= zero`, `*= scale`, each rounded to out_dtype.  out is [N][K] row-major. */
+LL_API int ll_get_weight(const uint8_t* qw, const void* scales, const void* zeros, int param_dtype, void* out,
+                  int out_dtype, int N, int K, int bits, int tile_cols, ll_stream stream);
+
+/* ref: ColBlockQuantizedLinear.forward, quantization.py:411-421 (both branches), any M, bits in
+ * {4,8}, any tile, fp32 or bf16 activations: y[M][N] = x[M][K] . W^T (+ bias), W as get_weight
+ * would produce it in the activation dtype, fp32 accumulation, one rounding on store.
+ * SIMT kernel: the always-correct path for shapes/dtypes the tensor-core kernels do not take. */
+LL_API int ll_qlinear_simt(const void* x, int act_dtype, int M, const uint8_t* qw, const void* scales, const void* zeros,
+                    int param_dtype, const void* bias, void* y, int N, int K, int bits, int tile_cols,
+                    ll_stream stream);
+
+/* ---------------------------------------------------------------------------------------
+ * int4 decode GEMV (M <= 8), bf16 activations.  Replaces the Triton launcher
+ * qlinear_4bit_weight (quantization.py:282-331: pads M to 256, per-row scales only) and the
+ * dequantise-then-F.linear fallback (quantization.py:420-421) for grouped scales.
+ * ------------------------------------------------------------------------------------- */
+
+/* One-time side table: sz[G][N] = bf16(scale) | bf16(128 + zero) << 16 (transposed so a group's
+ * parameters are contiguous along N).  status[0] (device int32) is set to 1 unless every
+ * (128 + zero) is exactly representable in bf16 (then the fast kernel is not bit-faithful to
+ * get_weight and the caller must use ll_qlinear_simt). */
+LL_API int ll_int4_prepare(const void* scales, const void* zeros, int param_dtype, uint32_t* sz, int N, int G,
+                    int32_t* status, ll_stream stream);
+
+#define LL_EPI_STORE 0    /* y = bf16(acc (+bias)) */
+#define LL_EPI_RESIDUAL 1 /* y (residual stream, in place) = bf16(y + bf16(acc)); ssq_out partials */
+#define LL_EPI_ROPE_KV 2  /* c_attn: RoPE on q,k; q -> y, k,v -> KV cache at pos[1] */
+#define LL_EPI_SWIGLU 3   /* y = bf16(bf16(silu(bf16(accA))) * bf16(accB)), accB from qw2/sz2 */
+
+#define LL_GEMV_PDL 1 /* launch with programmatic stream serialization (prologue overlap) */
+
+typedef struct ll_gemv_args {
+  const uint8_t* qw;   /* packed int4 [K/2][N] */
+  const uint32_t* sz;  /* [G][N] from ll_int4_prepare */
+  const uint8_t* qw2;  /* second matrix (LL_EPI_SWIGLU: c_fc2), same shape; else NULL */
+  const uint32_t* sz2;
+  int32_t N, K, group; /* group = k per scale group (K when per-row) */
+  int32_t M;           /* rows of x, 1..8 */
+  const void* x;       /* [M][K] bf16 */
+  /* optional fused RMSNorm on x (ref: model.py:276-283): x_used = bf16(w * bf16(x * r)),
+   * r from the ssq partials: mean = bf16(sum(ssq[m][:]) / K) */
+  const void* norm_weight; /* [K] bf16 or NULL */
+  const float* ssq;        /* [M][ssq_parts] partial sums of bf16(x*x) */
+  int32_t ssq_parts;
+  float eps;
+  int32_t epilogue;
+  int32_t flags;
+  void* y;          /* see LL_EPI_* ; [M][N] bf16 (ROPE_KV: q [M][N/3]) */
+  const void* bias; /* [N] bf16 or NULL (LL_EPI_STORE) */
+  float* ssq_out;   /* LL_EPI_RESIDUAL: [M][ceil(N/128)] */
+  /* LL_EPI_ROPE_KV (ref: model.py:204-228, 312-329) */
+  const float* rope;  /* [block_size][head_size/2][2] fp32 (cos, sin) */
+  const int32_t* pos; /* device int32[3]: rope position, cache slot, #valid slots */
+  void* k_cache;      /* [M][n_head][cache_len][head_size] bf16 */
+  void* v_cache;
+  int32_t n_head, head_size, cache_len;
+  /* split-K scratch (needed when the launch splits K across CTAs; see ll_int4_gemv_plan) */
+  float* partials;   /* [ksplit][nmat][M][N] fp32 */
+  int32_t* counters; /* [ceil(N/128)] int32, zero before first use; the kernel leaves them zero */
+  int32_t ksplit;    /* 0 = choose */
+} ll_gemv_args;
+
+/* Host query: the K split the library would choose for (N, K, group) and the scratch sizes. */
+LL_API int ll_int4_gemv_plan(int N, int K, int group, int nmat, int M, int32_t* ksplit, size_t* partial_bytes,
+                      size_t* counter_bytes);
+LL_API int ll_int4_gemv(const ll_gemv_args* args /* host */, ll_stream stream);
+
+/* ---------------------------------------------------------------------------------------
+ * model.py kernels
+ * ------------------------------------------------------------------------------------- */
+
+/* ref: RMSNorm.forward, model.py:276-283 - every intermediate rounded to the activation dtype. */
+LL_API int ll_rmsnorm(const void* x, const void* weight, void* y, int dtype, int rows, int dim, float eps, ll_stream stream);
+
+/* ref: wte lookup, model.py:110, fused with the sum-of-squares partials the first fused RMSNorm
+ * consumes: x[m][:] = wte[idx[m]][:]; ssq[m][p] = sum over 128-column chunk p of bf16(x*x). */
+LL_API int ll_embed_ssq(const void* wte, const int64_t* idx, void* x, float* ssq, int M, int dim, ll_stream stream);
+
+/* ref: apply_rope (model.py:312-329) on q and k of a fused qkv row + KV-cache write (model.py:218-228,
+ * in place - the ring slot replaces the reference's roll).  qkv [B][T][3E]; q_out [B][nh][T][hs];
+ * caches [B][nh][S][hs]; pos_ids[T] rope rows, slots[T] cache slots (device int32). */
+LL_API int ll_rope_kv_append(const void* qkv, const float* rope, const int32_t* pos_ids, const int32_t* slots, void* q_out,
+                      void* k_cache, void* v_cache, int dtype, int B, int T, int n_head, int head_size, int cache_len,
+                      ll_stream stream);
+
+/* ref: apply_rope, model.py:312-329 (standalone form): x, y [B][T][nh][hs]; rope [T][hs/2][2] fp32 rows
+ * already selected for the T positions.  fp32 rotation of interleaved pairs, rounded to dtype. */
+LL_API int ll_apply_rope(const void* x, const float* rope, void* y, int dtype, int B, int T, int n_head, int head_size,
+                  ll_stream stream);
+
+/* ref: F.scaled_dot_product_attention over the KV cache for ONE query token per sequence
+ * (model.py:237 with T=1): attends slots [0, pos[2]).  q [B][nh][hs]; y [B][nh*hs].
+ * Split along the cache (flash-decoding) with a deterministic last-arriver combine.
+ * scratch: float [B*nh*splits*(hs+2)], counters int32 [B*nh] (zero; left zero). */
+LL_API int ll_decode_attn(const void* q, const void* k_cache, const void* v_cache, const int32_t* pos, void* y, int dtype,
+                   int B, int n_head, int head_size, int cache_len, int max_splits, float* scratch,
+                   int32_t* counters, int flags, ll_stream stream);
+LL_API size_t ll_decode_attn_scratch_bytes(int B, int n_head, int head_size, int max_splits);
+
+/* ref: MLP.forward's silu(a) * b, model.py:258, rounded like torch (silu -> dtype, product -> dtype). */
+LL_API int ll_silu_mul(const void* a, const void* b, void* y, int dtype, size_t n, ll_stream stream);
+/* y = dtype(a + b) : the residual adds of Block.forward, model.py:172-173 */
+LL_API int ll_add(const void* a, const void* b, void* y, int dtype, size_t n, ll_stream stream);
+/* pos[0] += 1; pos[1] = pos[0] % cache_len; pos[2] = min(pos[0] + 1, cache_len): one decode step
+ * (ref: generate.py:77 input_pos advance + model.py:221-225 sliding window). */
+LL_API int ll_advance_pos(int32_t* pos, int cache_len, ll_stream stream);
+/* pos[0] = input_pos[0] (device int64, the caller's position tensor); pos[1], pos[2] as above.
+ * Lets LLaMA.forward(idx, max_seq_length, input_pos) honour an arbitrary input_pos without a
+ * host sync (ref: model.py:101-104 index_select by input_pos). */
+LL_API int ll_set_pos(int32_t* pos, const int64_t* input_pos, int cache_len, ll_stream stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LLB200_H */

@@ -1,0 +1,406 @@
+// model.py kernels around the quantized Linears: RMSNorm, embedding (+ sum-of-squares partials),
+// RoPE + in-place KV-cache write, split-KV decode attention, SwiGLU product, residual add.
+// ref: /root/reference/lit_llama/model.py:110, 162-175, 192-243, 257-260, 276-283, 312-329.
+// Every kernel mirrors torch's rounding points (each elementwise op rounds to the activation dtype).
+#include "common.cuh"
+
+namespace llb {
+namespace {
+
+// ---------------------------------------------------------------- RMSNorm (row N)
+template <typename T>
+__global__ void rmsnorm_kernel(const T* __restrict__ x, const T* __restrict__ w, T* __restrict__ y, int dim, float eps) {
+  __shared__ float red[32];
+  __shared__ float s_r;
+  const T* xr = x + (size_t)blockIdx.x * dim;
+  T* yr = y + (size_t)blockIdx.x * dim;
+  float ss = 0.f;
+  for (int i = threadIdx.x; i < dim; i += blockDim.x) {
+    const float v = dt<T>::ld(xr, i);
+    ss += dt<T>::rd(__fmul_rn(v, v));
+  }
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) t += red[i];
+    const float mean = dt<T>::rd(t * (1.0f / (float)dim));
+    s_r = dt<T>::rd(rsqrtf(dt<T>::rd(__fadd_rn(mean, eps))));
+  }
+  __syncthreads();
+  const float r = s_r;
+  for (int i = threadIdx.x; i < dim; i += blockDim.x) {
+    const float xn = dt<T>::rd(__fmul_rn(dt<T>::ld(xr, i), r));
+    dt<T>::st(yr, i, __fmul_rn(dt<T>::ld(w, i), xn));
+  }
+}
+
+// ---------------------------------------------------------------- embedding + ssq partials
+__global__ void embed_ssq_kernel(const __nv_bfloat16* __restrict__ wte, const int64_t* __restrict__ idx,
+                                 __nv_bfloat16* __restrict__ x, float* __restrict__ ssq, int dim, int nchunks) {
+  __shared__ float red[4];
+  const int m = blockIdx.y, chunk = blockIdx.x;
+  const int n = chunk * 128 + threadIdx.x;
+  float v = 0.f;
+  if (n < dim) {
+    const __nv_bfloat16 e = wte[(size_t)idx[m] * dim + n];
+    x[(size_t)m * dim + n] = e;
+    v = __bfloat162float(e);
+    v = bf16r(__fmul_rn(v, v));
+  }
+  v = warp_sum(v);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) ssq[m * nchunks + chunk] = ((red[0] + red[1]) + red[2]) + red[3];
+}
+
+// ---------------------------------------------------------------- RoPE + KV append (rows R, A)
+// grid (T, B*n_head), block head_size/2 threads
+template <typename T>
+__global__ void rope_kv_kernel(const T* __restrict__ qkv, const float* __restrict__ rope,
+                               const int32_t* __restrict__ pos_ids, const int32_t* __restrict__ slots,
+                               T* __restrict__ q_out, T* __restrict__ kc, T* __restrict__ vc, int Tn, int n_head,
+                               int hs, int S) {
+  const int t = blockIdx.x, bh = blockIdx.y, b = bh / n_head, head = bh % n_head;
+  const int E = n_head * hs;
+  const int i = threadIdx.x;  // pair index
+  if (i >= hs / 2) return;
+  const T* row = qkv + ((size_t)b * Tn + t) * 3 * E;
+  const float2 cs = *reinterpret_cast<const float2*>(rope + ((size_t)pos_ids[t] * (hs / 2) + i) * 2);
+  const int slot = slots[t];
+  const int d = 2 * i;
+  {
+    const float x0 = dt<T>::ld(row, head * hs + d), x1 = dt<T>::ld(row, head * hs + d + 1);
+    T* o = q_out + (((size_t)b * n_head + head) * Tn + t) * hs;
+    dt<T>::st(o, d, __fsub_rn(__fmul_rn(x0, cs.x), __fmul_rn(x1, cs.y)));
+    dt<T>::st(o, d + 1, __fadd_rn(__fmul_rn(x1, cs.x), __fmul_rn(x0, cs.y)));
+  }
+  {
+    const float x0 = dt<T>::ld(row, E + head * hs + d), x1 = dt<T>::ld(row, E + head * hs + d + 1);
+    T* o = kc + (((size_t)b * n_head + head) * S + slot) * hs;
+    dt<T>::st(o, d, __fsub_rn(__fmul_rn(x0, cs.x), __fmul_rn(x1, cs.y)));
+    dt<T>::st(o, d + 1, __fadd_rn(__fmul_rn(x1, cs.x), __fmul_rn(x0, cs.y)));
+  }
+  {
+    T* o = vc + (((size_t)b * n_head + head) * S + slot) * hs;
+    o[d] = row[2 * E + head * hs + d];
+    o[d + 1] = row[2 * E + head * hs + d + 1];
+  }
+}
+
+// ---------------------------------------------------------------- decode attention (row A, T=1)
+// grid (B*n_head, nsplit); 4 warps; a position is handled by 8 lanes (HS/8 elements each).
+template <typename T> struct vec_ld;
+template <> struct vec_ld<__nv_bfloat16> {
+  template <int EPL> static __device__ __forceinline__ void ld(const __nv_bfloat16* p, float (&o)[EPL]) {
+    if constexpr (EPL % 8 == 0) {
+#pragma unroll
+      for (int i = 0; i < EPL / 8; ++i) {
+        const uint4 r = *reinterpret_cast<const uint4*>(p + 8 * i);
+        const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          o[8 * i + 2 * j] = bf16_bits_to_f32(w[j] & 0xffff);
+          o[8 * i + 2 * j + 1] = bf16_bits_to_f32(w[j] >> 16);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < EPL / 4; ++i) {
+        const uint2 r = *reinterpret_cast<const uint2*>(p + 4 * i);
+        o[4 * i] = bf16_bits_to_f32(r.x & 0xffff); o[4 * i + 1] = bf16_bits_to_f32(r.x >> 16);
+        o[4 * i + 2] = bf16_bits_to_f32(r.y & 0xffff); o[4 * i + 3] = bf16_bits_to_f32(r.y >> 16);
+      }
+    }
+  }
+};
+template <> struct vec_ld<float> {
+  template <int EPL> static __device__ __forceinline__ void ld(const float* p, float (&o)[EPL]) {
+#pragma unroll
+    for (int i = 0; i < EPL / 4; ++i) {
+      const float4 r = *reinterpret_cast<const float4*>(p + 4 * i);
+      o[4 * i] = r.x; o[4 * i + 1] = r.y; o[4 * i + 2] = r.z; o[4 * i + 3] = r.w;
+    }
+  }
+};
+
+template <typename T, int HS>
+__global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ q, const T* __restrict__ kc,
+                                                          const T* __restrict__ vc, const int32_t* __restrict__ pos,
+                                                          T* __restrict__ y, int n_head, int S, int nsplit,
+                                                          float* __restrict__ scratch, int32_t* __restrict__ counters,
+                                                          int use_pdl) {
+  constexpr int EPL = HS / 8;
+  constexpr int NW = 4;
+  __shared__ float s_m[NW * 4], s_l[NW * 4];
+  __shared__ float s_o[NW * 4][HS];
+  __shared__ int s_last;
+  if (use_pdl) {
+    pdl_launch_dependents();
+    pdl_wait();
+  }
+  const int bh = blockIdx.x, split = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, lg = lane >> 3, li = lane & 7;
+  const int nvalid = min(pos[2], S);
+  const int per = (nvalid + nsplit - 1) / nsplit;
+  const int s0 = split * per, s1 = min(s0 + per, nvalid);
+  const float scale_log2 = rsqrtf((float)HS) * 1.4426950408889634f;
+
+  float qr[EPL];
+  vec_ld<T>::template ld<EPL>(q + (size_t)bh * HS + li * EPL, qr);
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) qr[e] *= scale_log2;
+
+  float m = -INFINITY, l = 0.f, o[EPL];
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) o[e] = 0.f;
+  const T* kbase = kc + (size_t)bh * S * HS + li * EPL;
+  const T* vbase = vc + (size_t)bh * S * HS + li * EPL;
+  for (int s = s0 + warp * 4 + lg; s < s1; s += 4 * NW) {
+    float kr[EPL], vr[EPL];
+    vec_ld<T>::template ld<EPL>(kbase + (size_t)s * HS, kr);
+    vec_ld<T>::template ld<EPL>(vbase + (size_t)s * HS, vr);
+    float sc = 0.f;
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) sc = fmaf(qr[e], kr[e], sc);
+    sc += __shfl_xor_sync(0xffffffffu, sc, 1);
+    sc += __shfl_xor_sync(0xffffffffu, sc, 2);
+    sc += __shfl_xor_sync(0xffffffffu, sc, 4);
+    const float mn = fmaxf(m, sc);
+    const float corr = exp2f(m - mn), pr = exp2f(sc - mn);
+    l = l * corr + pr;
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) o[e] = o[e] * corr + pr * vr[e];
+    m = mn;
+  }
+  // combine the 16 (warp, lane-group) partial states of this CTA in fixed order
+  if (li == 0) { s_m[warp * 4 + lg] = m; s_l[warp * 4 + lg] = l; }
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) s_o[warp * 4 + lg][li * EPL + e] = o[e];
+  __syncthreads();
+  float* my = scratch + ((size_t)bh * nsplit + split) * (HS + 2);
+  if (threadIdx.x < HS) {
+    float M = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < NW * 4; ++i) M = fmaxf(M, s_m[i]);
+    float L = 0.f, O = 0.f;
+    if (M > -INFINITY) {
+#pragma unroll
+      for (int i = 0; i < NW * 4; ++i) {
+        const float c = exp2f(s_m[i] - M);
+        L += s_l[i] * c;
+        O += s_o[i][threadIdx.x] * c;
+      }
+    }
+    if (nsplit == 1) {
+      dt<T>::st(y + (size_t)bh * HS, threadIdx.x, O / L);
+    } else {
+      my[2 + threadIdx.x] = O;
+      if (threadIdx.x == 0) { my[0] = M; my[1] = L; }
+    }
+  }
+  if (nsplit == 1) return;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(&counters[bh], 1) == nsplit - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (threadIdx.x < HS) {
+    const float* base = scratch + (size_t)bh * nsplit * (HS + 2);
+    float M = -INFINITY;
+    for (int i = 0; i < nsplit; ++i) M = fmaxf(M, __ldcg(base + i * (HS + 2)));
+    float L = 0.f, O = 0.f;
+    for (int i = 0; i < nsplit; ++i) {
+      const float mi = __ldcg(base + i * (HS + 2));
+      if (mi > -INFINITY) {
+        const float c = exp2f(mi - M);
+        L += __ldcg(base + i * (HS + 2) + 1) * c;
+        O += __ldcg(base + i * (HS + 2) + 2 + threadIdx.x) * c;
+      }
+    }
+    dt<T>::st(y + (size_t)bh * HS, threadIdx.x, O / L);
+  }
+  if (threadIdx.x == 0) counters[bh] = 0;
+}
+
+// ---------------------------------------------------------------- elementwise
+template <typename T>
+__global__ void silu_mul_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ y, size_t n) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const float av = dt<T>::ld(a, i);
+    const float s = dt<T>::rd(av / (1.0f + expf(-av)));
+    dt<T>::st(y, i, __fmul_rn(s, dt<T>::ld(b, i)));
+  }
+}
+template <typename T>
+__global__ void add_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ y, size_t n) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dt<T>::st(y, i, __fadd_rn(dt<T>::ld(a, i), dt<T>::ld(b, i)));
+}
+__global__ void advance_pos_kernel(int32_t* pos, int S) {
+  const int p = pos[0] + 1;
+  pos[0] = p;
+  pos[1] = p % S;
+  pos[2] = min(p + 1, S);
+}
+
+// standalone apply_rope (ref: model.py:312-329): x,y [B][T][nh][hs], rope [T][hs/2][2] fp32
+template <typename T>
+__global__ void apply_rope_kernel(const T* __restrict__ x, const float* __restrict__ rope, T* __restrict__ y, int Tn,
+                                  int n_head, int hs, size_t npairs) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npairs) return;
+  const int half = hs / 2;
+  const int pi = (int)(i % half);
+  const int t = (int)((i / half / n_head) % Tn);
+  const float2 cs = *reinterpret_cast<const float2*>(rope + ((size_t)t * half + pi) * 2);
+  const float x0 = dt<T>::ld(x, 2 * i), x1 = dt<T>::ld(x, 2 * i + 1);
+  dt<T>::st(y, 2 * i, __fsub_rn(__fmul_rn(x0, cs.x), __fmul_rn(x1, cs.y)));
+  dt<T>::st(y, 2 * i + 1, __fadd_rn(__fmul_rn(x1, cs.x), __fmul_rn(x0, cs.y)));
+}
+
+__global__ void set_pos_kernel(int32_t* pos, const int64_t* input_pos, int S) {
+  const int p = (int)input_pos[0];
+  pos[0] = p;
+  pos[1] = p % S;
+  pos[2] = min(p + 1, S);
+}
+
+}  // namespace
+}  // namespace llb
+
+using namespace llb;
+
+extern "C" {
+
+int ll_rmsnorm(const void* x, const void* w, void* y, int dtype, int rows, int dim, float eps, ll_stream stream) {
+  LL_CHECK_ARG(x && w && y && rows >= 0 && dim > 0, "bad rmsnorm arguments");
+  if (rows == 0) return LL_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int threads = dim >= 1024 ? 256 : 128;
+  if (dtype == LL_F32) rmsnorm_kernel<float><<<rows, threads, 0, st>>>((const float*)x, (const float*)w, (float*)y, dim, eps);
+  else if (dtype == LL_BF16) rmsnorm_kernel<__nv_bfloat16><<<rows, threads, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)w, (__nv_bfloat16*)y, dim, eps);
+  else {
+    set_error("rmsnorm: unsupported dtype %d", dtype);
+    return LL_ERR_UNSUPPORTED;
+  }
+  LL_LAUNCH_OK("rmsnorm_kernel");
+  return LL_OK;
+}
+
+int ll_embed_ssq(const void* wte, const int64_t* idx, void* x, float* ssq, int M, int dim, ll_stream stream) {
+  LL_CHECK_ARG(wte && idx && x && ssq && M > 0 && dim > 0, "bad embed arguments");
+  const int nchunks = (dim + 127) / 128;
+  embed_ssq_kernel<<<dim3(nchunks, M), 128, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)wte, idx, (__nv_bfloat16*)x, ssq, dim, nchunks);
+  LL_LAUNCH_OK("embed_ssq_kernel");
+  return LL_OK;
+}
+
+int ll_rope_kv_append(const void* qkv, const float* rope, const int32_t* pos_ids, const int32_t* slots, void* q_out,
+                      void* k_cache, void* v_cache, int dtype, int B, int T, int n_head, int head_size, int cache_len,
+                      ll_stream stream) {
+  LL_CHECK_ARG(qkv && rope && pos_ids && slots && q_out && k_cache && v_cache, "null pointer");
+  LL_CHECK_ARG(B > 0 && T > 0 && n_head > 0 && head_size > 0 && head_size % 2 == 0 && cache_len > 0, "bad shape");
+  LL_CHECK_ARG(head_size / 2 <= 1024 && (long)B * n_head <= 65535, "shape too large");
+  dim3 grid(T, B * n_head), block(((head_size / 2) + 31) / 32 * 32);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == LL_F32) rope_kv_kernel<float><<<grid, block, 0, st>>>((const float*)qkv, rope, pos_ids, slots, (float*)q_out, (float*)k_cache, (float*)v_cache, T, n_head, head_size, cache_len);
+  else if (dtype == LL_BF16) rope_kv_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16*)qkv, rope, pos_ids, slots, (__nv_bfloat16*)q_out, (__nv_bfloat16*)k_cache, (__nv_bfloat16*)v_cache, T, n_head, head_size, cache_len);
+  else {
+    set_error("rope_kv_append: unsupported dtype %d", dtype);
+    return LL_ERR_UNSUPPORTED;
+  }
+  LL_LAUNCH_OK("rope_kv_kernel");
+  return LL_OK;
+}
+
+size_t ll_decode_attn_scratch_bytes(int B, int n_head, int head_size, int max_splits) {
+  return (size_t)B * n_head * max_splits * (head_size + 2) * sizeof(float);
+}
+
+int ll_decode_attn(const void* q, const void* k_cache, const void* v_cache, const int32_t* pos, void* y, int dtype, int B,
+                   int n_head, int head_size, int cache_len, int max_splits, float* scratch, int32_t* counters,
+                   int flags, ll_stream stream) {
+  LL_CHECK_ARG(q && k_cache && v_cache && pos && y, "null pointer");
+  LL_CHECK_ARG(B > 0 && n_head > 0 && cache_len > 0 && max_splits >= 1 && max_splits <= 64, "bad shape");
+  if (max_splits > 1) LL_CHECK_ARG(scratch && counters, "split decode attention needs scratch and counters");
+  dim3 grid(B * n_head, max_splits), block(128);
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool pdl = (flags & LL_GEMV_PDL) != 0;
+#define ATTN(TT, HS)                                                                                              \
+  LL_CUDA(launch(decode_attn_kernel<TT, HS>, grid, block, 0, st, pdl, (const TT*)q, (const TT*)k_cache,          \
+                 (const TT*)v_cache, pos, (TT*)y, n_head, cache_len, max_splits, scratch, counters, pdl ? 1 : 0))
+  if (dtype == LL_BF16) {
+    if (head_size == 128) ATTN(__nv_bfloat16, 128);
+    else if (head_size == 64) ATTN(__nv_bfloat16, 64);
+    else if (head_size == 32) ATTN(__nv_bfloat16, 32);
+    else { set_error("decode_attn: head_size %d unsupported (32, 64, 128)", head_size); return LL_ERR_UNSUPPORTED; }
+  } else if (dtype == LL_F32) {
+    if (head_size == 128) ATTN(float, 128);
+    else if (head_size == 64) ATTN(float, 64);
+    else if (head_size == 32) ATTN(float, 32);
+    else { set_error("decode_attn: head_size %d unsupported (32, 64, 128)", head_size); return LL_ERR_UNSUPPORTED; }
+  } else {
+    set_error("decode_attn: unsupported dtype %d", dtype);
+    return LL_ERR_UNSUPPORTED;
+  }
+#undef ATTN
+  return LL_OK;
+}
+
+int ll_silu_mul(const void* a, const void* b, void* y, int dtype, size_t n, ll_stream stream) {
+  LL_CHECK_ARG(a && b && y, "null pointer");
+  if (n == 0) return LL_OK;
+  const unsigned blocks = (unsigned)((n + 255) / 256);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == LL_F32) silu_mul_kernel<float><<<blocks, 256, 0, st>>>((const float*)a, (const float*)b, (float*)y, n);
+  else if (dtype == LL_BF16) silu_mul_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)a, (const __nv_bfloat16*)b, (__nv_bfloat16*)y, n);
+  else { set_error("silu_mul: unsupported dtype %d", dtype); return LL_ERR_UNSUPPORTED; }
+  LL_LAUNCH_OK("silu_mul_kernel");
+  return LL_OK;
+}
+
+int ll_add(const void* a, const void* b, void* y, int dtype, size_t n, ll_stream stream) {
+  LL_CHECK_ARG(a && b && y, "null pointer");
+  if (n == 0) return LL_OK;
+  const unsigned blocks = (unsigned)((n + 255) / 256);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == LL_F32) add_kernel<float><<<blocks, 256, 0, st>>>((const float*)a, (const float*)b, (float*)y, n);
+  else if (dtype == LL_BF16) add_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)a, (const __nv_bfloat16*)b, (__nv_bfloat16*)y, n);
+  else { set_error("add: unsupported dtype %d", dtype); return LL_ERR_UNSUPPORTED; }
+  LL_LAUNCH_OK("add_kernel");
+  return LL_OK;
+}
+
+int ll_advance_pos(int32_t* pos, int cache_len, ll_stream stream) {
+  LL_CHECK_ARG(pos && cache_len > 0, "bad advance_pos arguments");
+  advance_pos_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(pos, cache_len);
+  LL_LAUNCH_OK("advance_pos_kernel");
+  return LL_OK;
+}
+
+int ll_apply_rope(const void* x, const float* rope, void* y, int dtype, int B, int T, int n_head, int head_size,
+                  ll_stream stream) {
+  LL_CHECK_ARG(x && rope && y && B > 0 && T > 0 && n_head > 0 && head_size > 0 && head_size % 2 == 0, "bad apply_rope arguments");
+  const size_t npairs = (size_t)B * T * n_head * (head_size / 2);
+  const unsigned blocks = (unsigned)((npairs + 255) / 256);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == LL_F32) apply_rope_kernel<float><<<blocks, 256, 0, st>>>((const float*)x, rope, (float*)y, T, n_head, head_size, npairs);
+  else if (dtype == LL_BF16) apply_rope_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)x, rope, (__nv_bfloat16*)y, T, n_head, head_size, npairs);
+  else if (dtype == LL_F16) apply_rope_kernel<__half><<<blocks, 256, 0, st>>>((const __half*)x, rope, (__half*)y, T, n_head, head_size, npairs);
+  else { set_error("apply_rope: unsupported dtype %d", dtype); return LL_ERR_UNSUPPORTED; }
+  LL_LAUNCH_OK("apply_rope_kernel");
+  return LL_OK;
+}
+
+int ll_set_pos(int32_t* pos, const int64_t* input_pos, int cache_len, ll_stream stream) {
+  LL_CHECK_ARG(pos && input_pos && cache_len > 0, "bad set_pos arguments");
+  set_pos_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(pos, input_pos, cache_len);
+  LL_LAUNCH_OK("set_pos_kernel");
+  return LL_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,163 @@
+"""ctypes binding of the llb200 C-ABI library (include/llb200.h).
+
+There is no CPU or PyTorch fallback behind these calls: if ``libllb200.so`` is missing the import
+of this module raises, and every wrapper raises ``RuntimeError`` with the library's message when a
+call fails.  Build the library with ``python lit-llama-ja_b200/build.py``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import torch
+
+_LIB_PATH = Path(__file__).resolve().parent / "libllb200.so"
+if not _LIB_PATH.exists():
+    raise ImportError(
+        f"{_LIB_PATH} not found: the CUDA kernels are not built. Run `python lit-llama-ja_b200/build.py` "
+        "(nvcc, sm_100a). There is no CPU fallback."
+    )
+lib = C.CDLL(str(_LIB_PATH))
+
+LL_F32, LL_BF16, LL_F16 = 0, 1, 2
+EPI_STORE, EPI_RESIDUAL, EPI_ROPE_KV, EPI_SWIGLU = 0, 1, 2, 3
+GEMV_PDL = 1
+
+_DT = {torch.float32: LL_F32, torch.bfloat16: LL_BF16, torch.float16: LL_F16}
+
+vp, i32, sz_t = C.c_void_p, C.c_int, C.c_size_t
+
+
+class GemvArgs(C.Structure):
+    """struct ll_gemv_args (include/llb200.h)."""
+    _fields_ = [
+        ("qw", vp), ("sz", vp), ("qw2", vp), ("sz2", vp),
+        ("N", C.c_int32), ("K", C.c_int32), ("group", C.c_int32), ("M", C.c_int32),
+        ("x", vp), ("norm_weight", vp), ("ssq", vp), ("ssq_parts", C.c_int32), ("eps", C.c_float),
+        ("epilogue", C.c_int32), ("flags", C.c_int32),
+        ("y", vp), ("bias", vp), ("ssq_out", vp),
+        ("rope", vp), ("pos", vp), ("k_cache", vp), ("v_cache", vp),
+        ("n_head", C.c_int32), ("head_size", C.c_int32), ("cache_len", C.c_int32),
+        ("partials", vp), ("counters", vp), ("ksplit", C.c_int32),
+    ]
+
+
+def _proto(name, argtypes, restype=C.c_int):
+    fn = getattr(lib, name)
+    fn.argtypes = argtypes
+    fn.restype = restype
+    return fn
+
+
+# every symbol include/llb200.h declares
+EXPORTS = {
+    "ll_last_error": ([], C.c_char_p),
+    "ll_abi_version": ([], C.c_int),
+    "ll_sm_count": ([], C.c_int),
+    "ll_pack_weight": ([vp, i32, vp, vp, i32, vp, i32, i32, i32, i32, vp], C.c_int),
+    "ll_get_weight": ([vp, vp, vp, i32, vp, i32, i32, i32, i32, i32, vp], C.c_int),
+    "ll_qlinear_simt": ([vp, i32, i32, vp, vp, vp, i32, vp, vp, i32, i32, i32, i32, vp], C.c_int),
+    "ll_int4_prepare": ([vp, vp, i32, vp, i32, i32, vp, vp], C.c_int),
+    "ll_int4_gemv_plan": ([i32, i32, i32, i32, i32, C.POINTER(C.c_int32), C.POINTER(sz_t), C.POINTER(sz_t)], C.c_int),
+    "ll_int4_gemv": ([C.POINTER(GemvArgs), vp], C.c_int),
+    "ll_rmsnorm": ([vp, vp, vp, i32, i32, i32, C.c_float, vp], C.c_int),
+    "ll_embed_ssq": ([vp, vp, vp, vp, i32, i32, vp], C.c_int),
+    "ll_rope_kv_append": ([vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp], C.c_int),
+    "ll_decode_attn": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp, i32, vp], C.c_int),
+    "ll_decode_attn_scratch_bytes": ([i32, i32, i32, i32], sz_t),
+    "ll_silu_mul": ([vp, vp, vp, i32, sz_t, vp], C.c_int),
+    "ll_add": ([vp, vp, vp, i32, sz_t, vp], C.c_int),
+    "ll_advance_pos": ([vp, i32, vp], C.c_int),
+    "ll_set_pos": ([vp, vp, i32, vp], C.c_int),
+    "ll_apply_rope": ([vp, vp, vp, i32, i32, i32, i32, i32, vp], C.c_int),
+}
+_fn = {name: _proto(name, a, r) for name, (a, r) in EXPORTS.items()}
+
+if _fn["ll_abi_version"]() != 1:
+    raise ImportError("libllb200.so ABI version mismatch; rebuild with lit-llama-ja_b200/build.py")
+
+
+def last_error() -> str:
+    return (_fn["ll_last_error"]() or b"").decode()
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise RuntimeError(f"{what} failed ({rc}): {last_error()}")
+
+
+def call(name: str, *args) -> None:
+    check(_fn[name](*args), name)
+
+
+def require_cuda(*tensors: torch.Tensor) -> None:
+    for t in tensors:
+        if t is not None and t.device.type != "cuda":
+            raise RuntimeError(
+                "lit-llama-ja_b200 computes on CUDA (sm_100a) only - there is no CPU fallback; "
+                f"got a tensor on {t.device}"
+            )
+
+
+def dtype_code(dt: torch.dtype) -> int:
+    try:
+        return _DT[dt]
+    except KeyError:
+        raise RuntimeError(f"unsupported dtype {dt}") from None
+
+
+def ptr(t) -> C.c_void_p:
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def stream() -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def gemv_plan(N: int, K: int, group: int, nmat: int, M: int):
+    ks, pb, cb = C.c_int32(), sz_t(), sz_t()
+    check(_fn["ll_int4_gemv_plan"](N, K, group, nmat, M, C.byref(ks), C.byref(pb), C.byref(cb)), "ll_int4_gemv_plan")
+    return ks.value, pb.value, cb.value
+
+
+def gemv(args: GemvArgs) -> None:
+    check(_fn["ll_int4_gemv"](C.byref(args), stream()), "ll_int4_gemv")
+
+
+def attn_scratch_bytes(B, n_head, hs, splits) -> int:
+    return _fn["ll_decode_attn_scratch_bytes"](B, n_head, hs, splits)
+
+
+class Workspace:
+    """Per-(device, stream) scratch for split-K partial sums, arrival counters and the
+    attention split states.  Kernels on one stream are ordered, so one buffer is shared by
+    every layer; counters are zeroed once and the kernels leave them zero."""
+
+    _cache: dict = {}
+
+    def __init__(self, device):
+        self.device = device
+        self.partials = torch.empty(1 << 20, dtype=torch.float32, device=device)
+        self.counters = torch.zeros(1024, dtype=torch.int32, device=device)
+        self.attn_scratch = torch.empty(1 << 18, dtype=torch.float32, device=device)
+        self.attn_counters = torch.zeros(4096, dtype=torch.int32, device=device)
+
+    @classmethod
+    def get(cls, device) -> "Workspace":
+        key = (device.index if device.index is not None else torch.cuda.current_device(),
+               torch.cuda.current_stream().cuda_stream)
+        ws = cls._cache.get(key)
+        if ws is None:
+            ws = cls._cache[key] = Workspace(device)
+        return ws
+
+    def ensure(self, partial_bytes=0, counter_bytes=0, attn_bytes=0, attn_counters=0):
+        if partial_bytes > self.partials.numel() * 4:
+            self.partials = torch.empty(partial_bytes // 4 + 1, dtype=torch.float32, device=self.device)
+        if counter_bytes > self.counters.numel() * 4:
+            self.counters = torch.zeros(counter_bytes // 4 + 1, dtype=torch.int32, device=self.device)
+        if attn_bytes > self.attn_scratch.numel() * 4:
+            self.attn_scratch = torch.empty(attn_bytes // 4 + 1, dtype=torch.float32, device=self.device)
+        if attn_counters > self.attn_counters.numel():
+            self.attn_counters = torch.zeros(attn_counters, dtype=torch.int32, device=self.device)
+        return self

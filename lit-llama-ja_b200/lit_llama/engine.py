@@ -1,0 +1,196 @@
+"""Fused single-token decode step for an int4 (GPTQ) / bf16 LLaMA, captured in a CUDA graph.
+
+One decode step = 1 embedding kernel + 5 kernels per block + 1 lm_head kernel, all launched with
+programmatic dependent launch so each GEMV's TMA weight stream starts while its predecessor drains:
+
+    embed_ssq                                    wte row + sum-of-squares partials
+    per block:
+      gemv c_attn   [RMSNorm prologue | RoPE + KV-cache write epilogue]      (ref model.py:204-228)
+      decode_attn   split-KV, deterministic combine                          (ref model.py:237)
+      gemv c_proj   [residual-add epilogue + ssq partials]                   (ref model.py:172, 242)
+      gemv c_fc1|c_fc2 [RMSNorm prologue | SwiGLU epilogue]                  (ref model.py:258)
+      gemv mlp.c_proj  [residual-add epilogue + ssq partials]                (ref model.py:173, 259)
+    gemv lm_head    [RMSNorm (ln_f) prologue]                                (ref model.py:125-127)
+
+Positions live in a device int32[3] (pos, ring slot, #valid slots) that ``ll_set_pos`` /
+``ll_advance_pos`` update, so the captured graph is replayed unchanged for every token.
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+
+from . import _native as N
+from .quantization import ColBlockQuantizedLinear
+
+
+def _env_flag(name: str, default: bool) -> bool:
+    v = os.environ.get(name)
+    return default if v is None else v not in ("0", "false", "False", "")
+
+
+class DecodeEngine:
+    MAX_BATCH = 8
+
+    @staticmethod
+    def eligible(model, B: int) -> bool:
+        cfg = model.config
+        if B > DecodeEngine.MAX_BATCH or cfg.n_embd % 128 != 0 or cfg.head_size not in (32, 64, 128):
+            return False
+        wte = model.transformer.wte.weight
+        if wte.device.type != "cuda" or wte.dtype != torch.bfloat16:
+            return False
+        lins = [model.lm_head]
+        for blk in model.transformer.h:
+            lins += [blk.attn.c_attn, blk.attn.c_proj, blk.mlp.c_fc1, blk.mlp.c_fc2, blk.mlp.c_proj]
+            if blk.rms_1.scale.dtype != torch.bfloat16:
+                return False
+        for lin in lins:
+            if not isinstance(lin, ColBlockQuantizedLinear) or lin.bias is not None:
+                return False
+            if lin.scales.dtype != torch.bfloat16 or lin.prepare() is None:
+                return False
+        for blk in model.transformer.h:
+            if blk.mlp.c_fc1.tile_cols != blk.mlp.c_fc2.tile_cols:
+                return False
+        return True
+
+    def __init__(self, model, B: int, max_seq_length: int):
+        cfg = model.config
+        self.model, self.B, self.S = model, B, max_seq_length
+        dev = model.transformer.wte.weight.device
+        E, H, V = cfg.n_embd, cfg.n_hidden, cfg.padded_vocab_size
+        self.nparts = E // 128
+        bf, f32, i32 = torch.bfloat16, torch.float32, torch.int32
+        self.tok = torch.zeros(B, dtype=torch.int64, device=dev)
+        self.pos = torch.zeros(3, dtype=i32, device=dev)
+        self.x = torch.zeros((B, E), dtype=bf, device=dev)        # residual stream
+        self.ssq = torch.zeros((B, self.nparts), dtype=f32, device=dev)
+        self.q = torch.zeros((B, E), dtype=bf, device=dev)
+        self.att = torch.zeros((B, E), dtype=bf, device=dev)
+        self.h = torch.zeros((B, H), dtype=bf, device=dev)
+        self.logits = torch.zeros((B, V), dtype=bf, device=dev)
+        self.rope = model._rope_f32
+        self.use_pdl = _env_flag("LLB200_PDL", True)
+        self.use_graph = _env_flag("LLB200_GRAPH", True)
+        self.n_launches = 0
+
+        # split plans + scratch (owned by the engine: nothing is allocated during capture)
+        pb_max, cb_max = 0, 0
+        self.plans = {}
+        for name, (n, k, g, nmat) in {
+            "attn": (3 * E, E, model.transformer.h[0].attn.c_attn.tile_cols, 1),
+            "proj": (E, E, model.transformer.h[0].attn.c_proj.tile_cols, 1),
+            "fc": (H, E, model.transformer.h[0].mlp.c_fc1.tile_cols, 2),
+            "down": (E, H, model.transformer.h[0].mlp.c_proj.tile_cols, 1),
+            "head": (V, E, model.lm_head.tile_cols, 1),
+        }.items():
+            ks, pb, cb = N.gemv_plan(n, k, g, nmat, B)
+            self.plans[name] = ks
+            pb_max, cb_max = max(pb_max, pb), max(cb_max, cb)
+        self.partials = torch.empty(pb_max // 4 + 16, dtype=f32, device=dev)
+        self.counters = torch.zeros(cb_max // 4 + 16, dtype=i32, device=dev)
+        nh, hs = cfg.n_head, cfg.head_size
+        self.splits = max(1, min(16, (2 * N._fn["ll_sm_count"]()) // max(1, B * nh), (max_seq_length + 63) // 64))
+        self.attn_scratch = torch.empty(N.attn_scratch_bytes(B, nh, hs, self.splits) // 4 + 16, dtype=f32, device=dev)
+        self.attn_counters = torch.zeros(B * nh, dtype=i32, device=dev)
+        self.graph = None
+        self._build_args()
+
+    def matches(self, B: int, max_seq_length: int) -> bool:
+        """True if this engine serves (B, max_seq_length).  After ``LLaMA.reset_cache()`` the model's
+        ``kv_caches`` list is empty: the engine's own cache tensors are re-attached (slots beyond the
+        #valid count are never read, so no zeroing is needed) and the captured graph stays valid."""
+        if B != self.B or max_seq_length != self.S:
+            return False
+        if not self.model.kv_caches:
+            self.model.kv_caches.extend(self.kv)
+        return self.model.kv_caches[0][0].data_ptr() == self._kv0_ptr
+
+    def reset(self):
+        pass
+
+    # ------------------------------------------------------------------ argument blocks
+    def _gemv_args(self, lin, x, y, epi, plan, norm=None, lin2=None):
+        a = N.GemvArgs()
+        a.qw, a.sz = lin.quant_weight.data_ptr(), lin._sz.data_ptr()
+        if lin2 is not None:
+            a.qw2, a.sz2 = lin2.quant_weight.data_ptr(), lin2._sz.data_ptr()
+        a.N, a.K, a.group, a.M = lin.out_features, lin.in_features, lin.tile_cols, self.B
+        a.x, a.y = x.data_ptr(), y.data_ptr()
+        if norm is not None:
+            a.norm_weight, a.ssq, a.ssq_parts, a.eps = norm.scale.data_ptr(), self.ssq.data_ptr(), self.nparts, norm.eps
+        a.epilogue, a.flags = epi, (N.GEMV_PDL if self.use_pdl else 0)
+        if epi == N.EPI_RESIDUAL:
+            a.ssq_out = self.ssq.data_ptr()
+        a.partials, a.counters, a.ksplit = self.partials.data_ptr(), self.counters.data_ptr(), self.plans[plan]
+        return a
+
+    def _build_args(self):
+        m, cfg = self.model, self.model.config
+        self.kv = list(m.kv_caches)
+        self._kv0_ptr = m.kv_caches[0][0].data_ptr()
+        self.layers = []
+        for i, blk in enumerate(m.transformer.h):
+            kc, vc = m.kv_caches[i]
+            a_attn = self._gemv_args(blk.attn.c_attn, self.x, self.q, N.EPI_ROPE_KV, "attn", norm=blk.rms_1)
+            a_attn.rope, a_attn.pos = self.rope.data_ptr(), self.pos.data_ptr()
+            a_attn.k_cache, a_attn.v_cache = kc.data_ptr(), vc.data_ptr()
+            a_attn.n_head, a_attn.head_size, a_attn.cache_len = cfg.n_head, cfg.head_size, self.S
+            a_proj = self._gemv_args(blk.attn.c_proj, self.att, self.x, N.EPI_RESIDUAL, "proj")
+            a_fc = self._gemv_args(blk.mlp.c_fc1, self.x, self.h, N.EPI_SWIGLU, "fc", norm=blk.rms_2, lin2=blk.mlp.c_fc2)
+            a_down = self._gemv_args(blk.mlp.c_proj, self.h, self.x, N.EPI_RESIDUAL, "down")
+            self.layers.append((a_attn, kc, vc, a_proj, a_fc, a_down))
+        self.a_head = self._gemv_args(m.lm_head, self.x, self.logits, N.EPI_STORE, "head", norm=m.transformer.ln_f)
+
+    # ------------------------------------------------------------------ one step
+    def _run_step(self):
+        cfg = self.model.config
+        st = N.stream()
+        wte = self.model.transformer.wte.weight
+        N.call("ll_embed_ssq", N.ptr(wte), N.ptr(self.tok), N.ptr(self.x), N.ptr(self.ssq), self.B, cfg.n_embd, st)
+        flags = N.GEMV_PDL if self.use_pdl else 0
+        n = 1
+        for a_attn, kc, vc, a_proj, a_fc, a_down in self.layers:
+            N.gemv(a_attn)
+            N.call("ll_decode_attn", N.ptr(self.q), N.ptr(kc), N.ptr(vc), N.ptr(self.pos), N.ptr(self.att), N.LL_BF16,
+                   self.B, cfg.n_head, cfg.head_size, self.S, self.splits, N.ptr(self.attn_scratch),
+                   N.ptr(self.attn_counters), flags, st)
+            N.gemv(a_proj)
+            N.gemv(a_fc)
+            N.gemv(a_down)
+            n += 5
+        N.gemv(self.a_head)
+        self.n_launches = n + 1
+
+    def _capture(self):
+        # warm up eagerly on a side stream (also sizes kernel attributes), then capture
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            self._run_step()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._run_step()
+        self.graph = g
+
+    def step(self):
+        """Run one decode step on the tokens in ``self.tok`` at the position in ``self.pos``."""
+        if not self.use_graph:
+            self._run_step()
+            return
+        if self.graph is None:
+            # the warm-up run inside _capture() writes a K/V row at the current slot and advances x;
+            # harmless: the replay below rewrites the same slot from the same token and position
+            self._capture()
+        self.graph.replay()
+
+    def forward_token(self, idx: torch.Tensor, input_pos: torch.Tensor) -> torch.Tensor:
+        """``LLaMA.forward(idx[B,1], max_seq_length, input_pos[1])`` (ref: model.py:84-128)."""
+        self.tok.copy_(idx.reshape(-1))
+        N.call("ll_set_pos", N.ptr(self.pos), N.ptr(input_pos.to(torch.int64)), self.S, N.stream())
+        self.step()
+        return self.logits.clone().view(self.B, 1, -1)

@@ -1,0 +1,201 @@
+"""Quantized Linear modules backed by hand-written sm_100a kernels (libllb200.so).
+
+Same module surface as the reference's ``lit_llama/quantization.py`` (buffer names, shapes,
+strides, state-dict keys, constructor protocol) so GPTQ checkpoints written by the reference's
+``quantize/gptq.py`` load unchanged.  All arithmetic runs on CUDA through the C-ABI in
+``include/llb200.h``; there is no Triton, no bitsandbytes and no CPU fallback.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from . import _native as N
+
+
+def _entries_per_byte(bits: int) -> int:
+    epb = 8 // bits
+    assert epb > 0 and epb * bits == 8, f"bits must be 1, 2, 4 or 8, got {bits}"
+    return epb
+
+
+class ColBlockQuantizedLinear(torch.nn.Module):
+    """GPTQ column-block quantized Linear (ref: lit_llama/quantization.py:338-421).
+
+    Buffers (identical to the reference): ``quant_weight`` uint8 ``[out, in/epb]`` with strides
+    ``(1, out)`` (memory is ``[in/epb][out]``), ``scales`` / ``zeros`` ``[out, ceil(in/tile)]`` in
+    the default dtype, ``bias`` ``[out]`` or ``None``.  ``bias`` has no default and must be a bool.
+    """
+
+    def __init__(self, in_features, out_features, bias: bool, *, bits, tile_cols):
+        super().__init__()
+        self.in_features = in_features
+        self.out_features = out_features
+        self.bits = bits
+        self.entries_per_byte = _entries_per_byte(bits)
+        assert in_features % self.entries_per_byte == 0
+        self.tile_cols = in_features if tile_cols == -1 else tile_cols
+        packed_t = torch.empty((in_features // self.entries_per_byte, out_features), dtype=torch.uint8)
+        self.register_buffer("quant_weight", packed_t.t())  # logical [out, in/epb], N-fastest storage
+        n_groups = (in_features + self.tile_cols - 1) // self.tile_cols
+        self.register_buffer("scales", torch.empty((out_features, n_groups)))
+        self.register_buffer("zeros", torch.empty((out_features, n_groups)))
+        assert isinstance(bias, bool)
+        self.register_buffer("bias", torch.empty((out_features,)) if bias else None)
+        self._sz = None        # [G][N] uint32 side table for the int4 GEMV (built lazily)
+        self._sz_key = None
+        self._sz_ok = False
+
+    # -- state-dict: accept a checkpoint whose group count differs from the constructor's
+    # (``quantization("gptq.int4")`` always builds per-row modules, ref utils.py:179-191; a
+    # group-128 checkpoint carries ``scales [out, in/128]``).
+    def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
+        s = state_dict.get(prefix + "scales")
+        if s is not None and tuple(s.shape) != tuple(self.scales.shape) and s.shape[0] == self.out_features:
+            g = s.shape[1]
+            if g > 0 and self.in_features % g == 0:
+                self.tile_cols = self.in_features // g
+                self.scales = torch.empty((self.out_features, g), dtype=self.scales.dtype, device=self.scales.device)
+                self.zeros = torch.empty_like(self.scales)
+        super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)
+        self._sz = None
+
+    def _apply(self, fn, *args, **kwargs):
+        # keep the reference's (1, out) strides of quant_weight across .to()/.cuda()
+        stride_ok = self.quant_weight.stride() == (1, self.out_features)
+        super()._apply(fn, *args, **kwargs)
+        if stride_ok and self.quant_weight.stride() != (1, self.out_features):
+            self.quant_weight = self.quant_weight.t().contiguous().t()
+        self._sz = None
+        return self
+
+    def _packed_ptr_ok(self):
+        qw = self.quant_weight
+        if qw.stride() != (1, self.out_features):
+            self.quant_weight = qw = qw.t().contiguous().t()
+        return qw
+
+    # ------------------------------------------------------------------ rows P, G
+    def pack_weight(self, weight):
+        """ref: quantization.py:374-388 - bit-exact (``/= scale``, ``+= zero``, clamp, truncate)."""
+        qw = self._packed_ptr_ok()
+        N.require_cuda(qw, self.scales, self.zeros)
+        weight = weight.to(device=qw.device).contiguous()
+        assert weight.shape == (self.out_features, self.in_features)
+        assert self.scales.dtype == self.zeros.dtype
+        N.call("ll_pack_weight", N.ptr(weight), N.dtype_code(weight.dtype), N.ptr(self.scales.contiguous()),
+               N.ptr(self.zeros.contiguous()), N.dtype_code(self.scales.dtype), N.ptr(qw), self.out_features,
+               self.in_features, self.bits, self.tile_cols, N.stream())
+        self._sz = None
+
+    def get_weight(self, dtype=torch.float):
+        """ref: quantization.py:390-409 - bit-exact de-quantisation to ``[out, in]`` in ``dtype``."""
+        qw = self._packed_ptr_ok()
+        N.require_cuda(qw, self.scales, self.zeros)
+        out = torch.empty((self.out_features, self.in_features), device=qw.device, dtype=dtype)
+        N.call("ll_get_weight", N.ptr(qw), N.ptr(self.scales.contiguous()), N.ptr(self.zeros.contiguous()),
+               N.dtype_code(self.scales.dtype), N.ptr(out), N.dtype_code(dtype), self.out_features,
+               self.in_features, self.bits, self.tile_cols, N.stream())
+        return out
+
+    # ------------------------------------------------------------------ int4 GEMV side table
+    def _fast_eligible(self) -> bool:
+        return (self.bits == 4 and self.out_features % 16 == 0 and self.in_features % 8 == 0
+                and self.tile_cols % 32 == 0 and self.in_features % self.tile_cols == 0
+                and self.scales.dtype == self.zeros.dtype)
+
+    def prepare(self):
+        """Build (once) the transposed ``[G][N]`` (scale, 128+zero) table the GEMV streams.
+        Returns it, or ``None`` when the layer cannot take the tensor-core GEMV bit-faithfully."""
+        key = (self.scales.data_ptr(), self.zeros.data_ptr(), self.scales._version, self.zeros._version)
+        if self._sz_key == key and self._sz is not None:
+            return self._sz if self._sz_ok else None
+        self._sz_key = key
+        if not self._fast_eligible():
+            self._sz, self._sz_ok = torch.empty(0), False
+            return None
+        dev = self.scales.device
+        G = self.scales.shape[1]
+        sz = torch.empty((G, self.out_features), dtype=torch.int32, device=dev)
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+        N.call("ll_int4_prepare", N.ptr(self.scales.contiguous()), N.ptr(self.zeros.contiguous()),
+               N.dtype_code(self.scales.dtype), N.ptr(sz), self.out_features, G, N.ptr(status), N.stream())
+        self._sz, self._sz_ok = sz, int(status.item()) == 0
+        return self._sz if self._sz_ok else None
+
+    # ------------------------------------------------------------------ row F
+    def forward(self, inp):
+        """ref: quantization.py:411-421.  M <= 8 bf16 rows: TMA-streamed int4 GEMV; small M in other
+        dtypes / bit widths: reference-semantics SIMT kernel; large M: dequant-GEMM."""
+        qw = self._packed_ptr_ok()
+        N.require_cuda(inp, qw)
+        K, Nout = self.in_features, self.out_features
+        assert inp.shape[-1] == K, "incompatible dimensions"
+        x = inp.reshape(-1, K)
+        if not x.is_contiguous():
+            x = x.contiguous()
+        M = x.shape[0]
+        out_shape = inp.shape[:-1] + (Nout,)
+        if M == 0:
+            return inp.new_empty(out_shape)
+        y = torch.empty((M, Nout), device=inp.device, dtype=inp.dtype)
+        if inp.dtype == torch.bfloat16 and M <= 8 and torch.cuda.is_current_stream_capturing() is False \
+                and self.prepare() is not None:
+            self._gemv(x, y)
+        elif inp.dtype == torch.bfloat16 and M <= 8 and self._sz is not None and self._sz_ok:
+            self._gemv(x, y)  # under graph capture: table must have been prepared before
+        elif M <= 16:
+            assert inp.dtype in (torch.float32, torch.bfloat16)
+            N.call("ll_qlinear_simt", N.ptr(x), N.dtype_code(x.dtype), M, N.ptr(qw), N.ptr(self.scales.contiguous()),
+                   N.ptr(self.zeros.contiguous()), N.dtype_code(self.scales.dtype), N.ptr(self.bias), N.ptr(y),
+                   Nout, K, self.bits, self.tile_cols, N.stream())
+        else:
+            y = dequant_gemm(self, x)
+        return y.reshape(out_shape)
+
+    def _gemv(self, x, y, *, pdl=False):
+        ws = N.Workspace.get(x.device)
+        M = x.shape[0]
+        ks, pb, cb = N.gemv_plan(self.out_features, self.in_features, self.tile_cols, 1, M)
+        ws.ensure(pb, cb)
+        a = N.GemvArgs()
+        a.qw, a.sz = self.quant_weight.data_ptr(), self._sz.data_ptr()
+        a.N, a.K, a.group, a.M = self.out_features, self.in_features, self.tile_cols, M
+        a.x, a.y = x.data_ptr(), y.data_ptr()
+        a.bias = 0 if self.bias is None else self.bias.data_ptr()
+        a.epilogue, a.flags = N.EPI_STORE, (N.GEMV_PDL if pdl else 0)
+        a.partials, a.counters, a.ksplit = ws.partials.data_ptr(), ws.counters.data_ptr(), ks
+        N.gemv(a)
+
+
+def dequant_gemm(lin: ColBlockQuantizedLinear, x: torch.Tensor) -> torch.Tensor:
+    """Large-M path (prefill): materialise W in the activation dtype with the bit-exact unpack
+    kernel and run the dense GEMM - exactly the reference's fallback branch (quantization.py:420-421).
+    The dense GEMM is a plain library GEMM; the tcgen05 dequant-GEMM replaces it where built."""
+    w = lin.get_weight(dtype=x.dtype)
+    return torch.nn.functional.linear(x, w, lin.bias)
+
+
+def qlinear_4bit_weight(inp, weight, scales, zeros):
+    """ref: quantization.py:282-331 (Triton launcher) - same signature: ``weight`` is the
+    ``[N, K/2]`` uint8 buffer with strides (1, N), ``scales``/``zeros`` are ``[N, 1]``.  Bias is not
+    applied, as in the reference."""
+    assert scales.shape == (weight.shape[0], 1) and zeros.shape == (weight.shape[0], 1)
+    K = weight.shape[1] * 2
+    assert inp.shape[-1] == K, "incompatible dimensions"
+    lin = ColBlockQuantizedLinear.__new__(ColBlockQuantizedLinear)
+    torch.nn.Module.__init__(lin)
+    lin.in_features, lin.out_features, lin.bits, lin.entries_per_byte, lin.tile_cols = K, weight.shape[0], 4, 2, K
+    lin.quant_weight, lin.scales, lin.zeros, lin.bias = weight, scales, zeros, None
+    lin._sz = lin._sz_key = None
+    lin._sz_ok = False
+    return lin(inp)
+
+
+class Linear8bitLt(torch.nn.Linear):
+    """LLM.int8() Linear (ref: quantization.py:36-75, wrapping bitsandbytes).  Placeholder until the
+    sm_100a int8 kernels land: constructing it fails loudly rather than falling back."""
+
+    def __init__(self, *args, **kwargs):
+        raise NotImplementedError("llm.int8 kernels are not built yet in this revision")
