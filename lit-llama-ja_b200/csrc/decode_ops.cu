@@ -146,6 +146,7 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
   const int per = (nvalid + nsplit - 1) / nsplit;
   const int s0 = split * per, s1 = min(s0 + per, nvalid);
   const float scale_log2 = rsqrtf((float)HS) * 1.4426950408889634f;
+  const unsigned gmask = 0xffu << (lg * 8);
 
   float qr[EPL];
   vec_ld<T>::template ld<EPL>(q + (size_t)bh * HS + li * EPL, qr);
@@ -164,9 +165,9 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
     float sc = 0.f;
 #pragma unroll
     for (int e = 0; e < EPL; ++e) sc = fmaf(qr[e], kr[e], sc);
-    sc += __shfl_xor_sync(0xffffffffu, sc, 1);
-    sc += __shfl_xor_sync(0xffffffffu, sc, 2);
-    sc += __shfl_xor_sync(0xffffffffu, sc, 4);
+    sc += __shfl_xor_sync(gmask, sc, 1);   // the 8 lanes of a group share a trip count; groups do not
+    sc += __shfl_xor_sync(gmask, sc, 2);
+    sc += __shfl_xor_sync(gmask, sc, 4);
     const float mn = fmaxf(m, sc);
     const float corr = exp2f(m - mn), pr = exp2f(sc - mn);
     l = l * corr + pr;

@@ -86,8 +86,13 @@ def check(rc: int, what: str) -> None:
         raise RuntimeError(f"{what} failed ({rc}): {last_error()}")
 
 
+LAUNCHES = 0   # kernels launched through this binding (bench.py's gpu_launches claim)
+
+
 def call(name: str, *args) -> None:
+    global LAUNCHES
     check(_fn[name](*args), name)
+    LAUNCHES += 1
 
 
 def require_cuda(*tensors: torch.Tensor) -> None:
@@ -121,6 +126,8 @@ def gemv_plan(N: int, K: int, group: int, nmat: int, M: int):
 
 
 def gemv(args: GemvArgs) -> None:
+    global LAUNCHES
+    LAUNCHES += 1
     check(_fn["ll_int4_gemv"](C.byref(args), stream()), "ll_int4_gemv")
 
 

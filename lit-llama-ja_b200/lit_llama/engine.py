@@ -75,6 +75,7 @@ class DecodeEngine:
         self.use_pdl = _env_flag("LLB200_PDL", True)
         self.use_graph = _env_flag("LLB200_GRAPH", True)
         self.n_launches = 0
+        self.n_replays = 0
 
         # split plans + scratch (owned by the engine: nothing is allocated during capture)
         pb_max, cb_max = 0, 0
@@ -187,6 +188,7 @@ class DecodeEngine:
             # harmless: the replay below rewrites the same slot from the same token and position
             self._capture()
         self.graph.replay()
+        self.n_replays += 1
 
     def forward_token(self, idx: torch.Tensor, input_pos: torch.Tensor) -> torch.Tensor:
         """``LLaMA.forward(idx[B,1], max_seq_length, input_pos[1])`` (ref: model.py:84-128)."""

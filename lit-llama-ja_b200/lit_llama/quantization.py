@@ -199,3 +199,48 @@ class Linear8bitLt(torch.nn.Linear):
 
     def __init__(self, *args, **kwargs):
         raise NotImplementedError("llm.int8 kernels are not built yet in this revision")
+
+
+# --------------------------------------------------------------------------------------- row Z
+def find_params_weight(x: torch.Tensor, maxq: int):
+    """ref: GPTQQuantizer.find_params_weight, quantization.py:474-511 (perchannel, asymmetric):
+    per-row ``scale = (max(x,0) - min(x,0)) / maxq``, ``zero = round(-xmin / scale)``; an all-zero
+    row uses (-1, +1).  Returns ``[rows, 1]`` tensors.  Device-agnostic torch ops (load-time)."""
+    x = x.flatten(1)
+    zero_t = torch.zeros(x.shape[0], device=x.device, dtype=x.dtype)
+    xmin = torch.minimum(x.amin(1), zero_t)
+    xmax = torch.maximum(x.amax(1), zero_t)
+    dead = (xmin == 0) & (xmax == 0)
+    xmin = torch.where(dead, torch.full_like(xmin, -1), xmin)
+    xmax = torch.where(dead, torch.full_like(xmax, +1), xmax)
+    scale = (xmax - xmin) / maxq
+    zero = torch.round(-xmin / scale)
+    return scale.reshape(-1, 1), zero.reshape(-1, 1)
+
+
+def quantize_weight(x, scale, zero, maxq):
+    """ref: GPTQQuantizer.quantize_weight, quantization.py:468-472 - snap to the grid, de-quantised."""
+    q = torch.clamp(torch.round(x / scale) + zero, 0, maxq)
+    return scale * (q - zero)
+
+
+@torch.no_grad()
+def rtn_quantize_(lin: ColBlockQuantizedLinear, weight: torch.Tensor) -> ColBlockQuantizedLinear:
+    """Round-to-nearest quantisation of ``weight`` into ``lin`` (per group of ``lin.tile_cols``):
+    parameters from ``find_params_weight``, on-grid weights from ``quantize_weight``, bytes from
+    ``pack_weight`` - the grouped fixture of SURVEY 8c/8d, all on the module's device."""
+    maxq = 2 ** lin.bits - 1
+    w = weight.to(device=lin.quant_weight.device, dtype=torch.float32)
+    n, k = w.shape
+    t = lin.tile_cols
+    assert k % t == 0
+    wg = w.view(n, k // t, t)
+    s, z = find_params_weight(wg.reshape(-1, t), maxq)
+    s, z = s.view(n, k // t), z.view(n, k // t)
+    lin.scales.copy_(s)
+    lin.zeros.copy_(z)
+    # de-quantised on-grid weights with the parameters as stored (possibly rounded to bf16)
+    s_st, z_st = lin.scales.float().unsqueeze(-1), lin.zeros.float().unsqueeze(-1)
+    q = quantize_weight(wg, s_st, z_st, maxq).view(n, k)
+    lin.pack_weight(q.to(lin.scales.dtype))
+    return lin

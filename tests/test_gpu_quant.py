@@ -73,10 +73,14 @@ def test_pack_unpack_random_large_vs_oracle(bits, tile):
     ref = OQ.pack_weight(Q, s, z, bits, tile)
     assert np.array_equal(lin.quant_weight.cpu().numpy(), ref)
     assert np.array_equal(lin.get_weight().cpu().numpy(), OQ.get_weight(ref, s, z, bits, tile))
-    # round trip: codes survive pack -> unpack -> pack
+    # round trip pack(get_weight()): same bytes as the oracle's round trip (the reference's truncation
+    # makes it non-idempotent for some 8-bit codes - reproduced, not "fixed")
     lin2 = make_lin(N, K, bits, tile, s, z, "fp32")
     lin2.pack_weight(lin.get_weight())
-    assert torch.equal(lin2.quant_weight, lin.quant_weight)
+    rt = OQ.pack_weight(OQ.get_weight(ref, s, z, bits, tile), s, z, bits, tile)
+    assert np.array_equal(lin2.quant_weight.cpu().numpy(), rt)
+    if bits == 4:
+        assert np.array_equal(rt, ref)
 
 
 def _bf16_layer(N, K, tile, seed):
