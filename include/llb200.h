@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define LL_ABI_VERSION 1
+#define LL_ABI_VERSION 2
 
 #define LL_OK 0
 #define LL_ERR_ARG (-1)         /* bad shape / dtype / null pointer */
@@ -77,27 +77,37 @@ LL_API int ll_qlinear_simt(const void* x, int act_dtype, int M, const uint8_t* q
  * int4 decode GEMV (M <= 8), bf16 activations.  Replaces the Triton launcher
  * qlinear_4bit_weight (quantization.py:282-331: pads M to 256, per-row scales only) and the
  * dequantise-then-F.linear fallback (quantization.py:420-421) for grouped scales.
+ *
+ * The kernel streams a one-time REPACK of the checkpoint bytes ("stream"): blocks of
+ * 16 output columns x KB input features (KB = 128, 64 or 32 = gcd-style divisor of the group
+ * size), each block = the 32 lanes' mma.m16n8k16 A-fragments in issue order followed by the
+ * block's 16 (scale, -(16+zero)) bf16 pairs.  Blocks are ordered (tile, k-block), k fastest,
+ * so any contiguous range of work items is one contiguous byte range (1-D bulk TMA).
+ * Arithmetic: y = sum_blocks scale * (sum_k (16+q) x_k - (16+zero) sum_k x_k), products exact,
+ * fp32 accumulation: the exact (q - zero) * scale of the reference's Triton kernel
+ * (quantization.py:247-251) without its TF32 rounding or the fallback's bf16 weight rounding.
  * ------------------------------------------------------------------------------------- */
 
-/* One-time side table: sz[G][N] = bf16(scale) | bf16(128 + zero) << 16 (transposed so a group's
- * parameters are contiguous along N).  status[0] (device int32) is set to 1 unless every
- * (128 + zero) is exactly representable in bf16 (then the fast kernel is not bit-faithful to
- * get_weight and the caller must use ll_qlinear_simt). */
-LL_API int ll_int4_prepare(const void* scales, const void* zeros, int param_dtype, uint32_t* sz, int N, int G,
-                    int32_t* status, ll_stream stream);
+/* bytes of the repacked stream for an [N][K] int4 matrix with scale groups of `group` columns
+ * (group = K for per-row); 0 if the shape is not supported by the GEMV (use ll_qlinear_simt). */
+LL_API size_t ll_int4_stream_bytes(int N, int K, int group);
+
+/* One-time repack: qw (checkpoint layout) + scales/zeros [N][K/group] -> stream.  status[0]
+ * (device int32) is set to 1 unless every scale and every (16 + zero) is exactly representable
+ * in bf16 (then the caller must use ll_qlinear_simt). */
+LL_API int ll_int4_prepare(const uint8_t* qw, const void* scales, const void* zeros, int param_dtype, uint8_t* stream_out,
+                    int N, int K, int group, int32_t* status, ll_stream stream);
 
 #define LL_EPI_STORE 0    /* y = bf16(acc (+bias)) */
 #define LL_EPI_RESIDUAL 1 /* y (residual stream, in place) = bf16(y + bf16(acc)); ssq_out partials */
 #define LL_EPI_ROPE_KV 2  /* c_attn: RoPE on q,k; q -> y, k,v -> KV cache at pos[1] */
-#define LL_EPI_SWIGLU 3   /* y = bf16(bf16(silu(bf16(accA))) * bf16(accB)), accB from qw2/sz2 */
+#define LL_EPI_SWIGLU 3   /* y = bf16(bf16(silu(bf16(accA))) * bf16(accB)), accB from w2 */
 
 #define LL_GEMV_PDL 1 /* launch with programmatic stream serialization (prologue overlap) */
 
 typedef struct ll_gemv_args {
-  const uint8_t* qw;   /* packed int4 [K/2][N] */
-  const uint32_t* sz;  /* [G][N] from ll_int4_prepare */
-  const uint8_t* qw2;  /* second matrix (LL_EPI_SWIGLU: c_fc2), same shape; else NULL */
-  const uint32_t* sz2;
+  const uint8_t* w;    /* repacked stream from ll_int4_prepare */
+  const uint8_t* w2;   /* second matrix (LL_EPI_SWIGLU: c_fc2), same shape; else NULL */
   int32_t N, K, group; /* group = k per scale group (K when per-row) */
   int32_t M;           /* rows of x, 1..8 */
   const void* x;       /* [M][K] bf16 */
@@ -111,21 +121,22 @@ typedef struct ll_gemv_args {
   int32_t flags;
   void* y;          /* see LL_EPI_* ; [M][N] bf16 (ROPE_KV: q [M][N/3]) */
   const void* bias; /* [N] bf16 or NULL (LL_EPI_STORE) */
-  float* ssq_out;   /* LL_EPI_RESIDUAL: [M][ceil(N/128)] */
+  float* ssq_out;   /* LL_EPI_RESIDUAL: [M][N/16] (one partial per 16-column tile) */
   /* LL_EPI_ROPE_KV (ref: model.py:204-228, 312-329) */
   const float* rope;  /* [block_size][head_size/2][2] fp32 (cos, sin) */
   const int32_t* pos; /* device int32[3]: rope position, cache slot, #valid slots */
   void* k_cache;      /* [M][n_head][cache_len][head_size] bf16 */
   void* v_cache;
   int32_t n_head, head_size, cache_len;
-  /* split-K scratch (needed when the launch splits K across CTAs; see ll_int4_gemv_plan) */
-  float* partials;   /* [ksplit][nmat][M][N] fp32 */
-  int32_t* counters; /* [ceil(N/128)] int32, zero before first use; the kernel leaves them zero */
-  int32_t ksplit;    /* 0 = choose */
+  /* cross-CTA scratch for tiles whose k range is shared by several CTAs (see ll_int4_gemv_plan) */
+  float* partials;
+  int32_t* counters; /* zero before first use; the kernel leaves them zero */
+  int32_t grid;      /* 0 = one CTA per SM; >0 forces the CTA count (tests) */
 } ll_gemv_args;
 
-/* Host query: the K split the library would choose for (N, K, group) and the scratch sizes. */
-LL_API int ll_int4_gemv_plan(int N, int K, int group, int nmat, int M, int32_t* ksplit, size_t* partial_bytes,
+/* Host query: scratch sizes for (N, K, group, nmat, M) at the CTA count the library would use
+ * (or `grid` if > 0).  Returns LL_ERR_UNSUPPORTED when the shape does not fit the kernel. */
+LL_API int ll_int4_gemv_plan(int N, int K, int group, int nmat, int M, int grid, size_t* partial_bytes,
                       size_t* counter_bytes);
 LL_API int ll_int4_gemv(const ll_gemv_args* args /* host */, ll_stream stream);
 
@@ -137,7 +148,7 @@ LL_API int ll_int4_gemv(const ll_gemv_args* args /* host */, ll_stream stream);
 LL_API int ll_rmsnorm(const void* x, const void* weight, void* y, int dtype, int rows, int dim, float eps, ll_stream stream);
 
 /* ref: wte lookup, model.py:110, fused with the sum-of-squares partials the first fused RMSNorm
- * consumes: x[m][:] = wte[idx[m]][:]; ssq[m][p] = sum over 128-column chunk p of bf16(x*x). */
+ * consumes: x[m][:] = wte[idx[m]][:]; ssq[m][p] = sum over 16-column tile p of bf16(x*x). */
 LL_API int ll_embed_ssq(const void* wte, const int64_t* idx, void* x, float* ssq, int M, int dim, ll_stream stream);
 
 /* ref: apply_rope (model.py:312-329) on q and k of a fused qkv row + KV-cache write (model.py:218-228,

@@ -38,10 +38,10 @@ __global__ void rmsnorm_kernel(const T* __restrict__ x, const T* __restrict__ w,
 
 // ---------------------------------------------------------------- embedding + ssq partials
 __global__ void embed_ssq_kernel(const __nv_bfloat16* __restrict__ wte, const int64_t* __restrict__ idx,
-                                 __nv_bfloat16* __restrict__ x, float* __restrict__ ssq, int dim, int nchunks) {
-  __shared__ float red[4];
-  const int m = blockIdx.y, chunk = blockIdx.x;
-  const int n = chunk * 128 + threadIdx.x;
+                                 __nv_bfloat16* __restrict__ x, float* __restrict__ ssq, int dim, int nparts) {
+  // one sum-of-squares partial per 16 columns (the int4 GEMV's tile width)
+  const int m = blockIdx.y;
+  const int n = blockIdx.x * 128 + threadIdx.x;
   float v = 0.f;
   if (n < dim) {
     const __nv_bfloat16 e = wte[(size_t)idx[m] * dim + n];
@@ -49,10 +49,12 @@ __global__ void embed_ssq_kernel(const __nv_bfloat16* __restrict__ wte, const in
     v = __bfloat162float(e);
     v = bf16r(__fmul_rn(v, v));
   }
-  v = warp_sum(v);
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
-  __syncthreads();
-  if (threadIdx.x == 0) ssq[m * nchunks + chunk] = ((red[0] + red[1]) + red[2]) + red[3];
+  v += __shfl_xor_sync(0xffffffffu, v, 8);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  const int part = n >> 4;
+  if ((threadIdx.x & 15) == 0 && part < nparts) ssq[m * nparts + part] = v;
 }
 
 // ---------------------------------------------------------------- RoPE + KV append (rows R, A)
@@ -293,9 +295,9 @@ int ll_rmsnorm(const void* x, const void* w, void* y, int dtype, int rows, int d
 }
 
 int ll_embed_ssq(const void* wte, const int64_t* idx, void* x, float* ssq, int M, int dim, ll_stream stream) {
-  LL_CHECK_ARG(wte && idx && x && ssq && M > 0 && dim > 0, "bad embed arguments");
+  LL_CHECK_ARG(wte && idx && x && ssq && M > 0 && dim > 0 && dim % 16 == 0, "bad embed arguments (dim must be a multiple of 16)");
   const int nchunks = (dim + 127) / 128;
-  embed_ssq_kernel<<<dim3(nchunks, M), 128, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)wte, idx, (__nv_bfloat16*)x, ssq, dim, nchunks);
+  embed_ssq_kernel<<<dim3(nchunks, M), 128, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)wte, idx, (__nv_bfloat16*)x, ssq, dim, dim / 16);
   LL_LAUNCH_OK("embed_ssq_kernel");
   return LL_OK;
 }

@@ -1,60 +1,57 @@
-// int4 (GPTQ column-block) decode GEMV for sm_100a: y[M<=8][N] = x[M][K] . dequant(qw)^T
+// int4 (GPTQ column-block) decode GEMV for sm_100a, v2: y[M<=8][N] = x[M][K] . dequant(W)^T
 //
 // Replaces the reference's Triton launcher (ref: lit_llama/quantization.py:282-331, which pads
 // M=1 to 256 rows and reads every packed byte twice) and its dequantise-then-F.linear fallback
 // (ref: quantization.py:390-421) for batch-1..8 decode.
 //
-// Design (B200-first; HBM-bound integer/byte work, no reshaping into a big GEMM):
-//  * The packed matrix is used IN PLACE in the checkpoint's layout: memory [K/2][N] bytes,
-//    N fastest; byte (r, n) holds k=2r (low nibble) and k=2r+1 (high nibble).
-//  * Work unit = (matrix, 128-column chunk, K split).  A persistent grid (<= 2 CTAs/SM) walks
-//    units round-robin.  One producer warp streams [TILE_ROWS x 128 B] weight tiles with 2-D
-//    TMA (128B swizzle, L2 evict-first) plus the group's 512-byte scale/zero row with a 1-D bulk
-//    copy into a per-consumer-warp ring of shared-memory slots, gated by mbarriers.  Weights do
-//    not depend on the previous kernel, so under programmatic dependent launch the producer
-//    starts streaming while the previous kernel is still draining.
-//  * Consumer warps: conflict-free LDS.128 of two packed rows, nibble -> bf16 with the
-//    0x4300 magic (128+q exact), HSUB2 (128+zero) and HMUL2 scale - bit-identical to
-//    get_weight(bf16) - then mma.sync m16n8k16 (bf16 x bf16 -> fp32) with the weights as the
-//    A operand: a packed byte's (k, k+1) pair for one column n IS an A-fragment register, so no
-//    shuffles.  x sits in shared memory pre-permuted as B fragments; the 8 MMA columns carry up
-//    to 8 batch rows for free.
-//  * Cross-warp reduction in shared memory (fixed order); split-K partials go to a global
-//    scratch and the LAST-arriving CTA of a chunk sums them in split order (deterministic,
-//    self-resetting counters) and runs the fused epilogue: plain store, residual add (+ RMSNorm
-//    sum-of-squares partials for the next kernel), RoPE + KV-cache write (c_attn), or SwiGLU
-//    (c_fc1/c_fc2 as two matrices of one launch).
-//  * Optional fused RMSNorm prologue while staging x (ref: model.py:276-283 rounding steps).
-#include <mutex>
-#include <unordered_map>
-
+// Design (B200-first; HBM-bound byte work, no reshaping into a big GEMM):
+//  * One-time repack (ll_int4_prepare) of the checkpoint bytes into a fragment-ordered STREAM of
+//    blocks: 16 output columns x KB input features (KB = 128/64/32), k-blocks fastest.  A block is
+//    the 32 lanes' mma.m16n8k16 A-fragment words in issue order (one 32-bit word = one MMA's
+//    A fragment = 8 nibbles placed at bit offsets 3+4i so that `(w >> 4i) & 0x00780078 | 0x41804180`
+//    IS the bf16x2 register holding (16+q, 16+q')), followed by the block's 16 (scale, -(16+zero))
+//    bf16 pairs.  7 ALU instructions per 8 weights, no per-weight scale/zero arithmetic.
+//  * Work item = one block.  Items are split evenly and CONTIGUOUSLY over one CTA per SM
+//    (stream-K), so a CTA's whole share is a contiguous byte range: one producer thread streams it
+//    with 1-D bulk TMA copies (L2 evict-first) into a shared-memory ring of chunks gated by
+//    mbarriers.  Weights do not depend on the previous kernel: under programmatic dependent launch
+//    the next GEMV's CTA co-resides (<= 110 KB smem each) and fills its ring while this one computes.
+//  * Consumer warps take one block per chunk each: LDS.128 of fragment words, dequant to bf16 by
+//    LOP3/SHF, mma.sync m16n8k16 (bf16 x bf16 -> fp32) with the weights as the A operand and up to
+//    8 batch rows of x as the B columns.  Per block: acc starts at -(16+zero)*sum(x_block), ends as
+//    sum (q-zero) x, and is folded into the running column sums with one FFMA by the scale.
+//  * x is staged once per CTA in shared memory in natural order (optionally through the fused
+//    RMSNorm, ref model.py:276-283 rounding steps) together with its per-block sums.
+//  * Fixed-order reduction across warps in shared memory; tiles whose k range is shared by several
+//    CTAs go through a global scratch and the LAST-arriving contributor sums them in contributor
+//    order (deterministic, self-resetting counters) and runs the fused epilogue: plain store,
+//    residual add (+ RMSNorm sum-of-squares partials for the next kernel), RoPE + KV-cache write
+//    (c_attn), or SwiGLU (c_fc1/c_fc2 as two matrices of one launch).
 #include "common.cuh"
 
 namespace llb {
 namespace {
 
-constexpr int CHUNK = 128;  // columns (= packed bytes per row segment) per unit
 constexpr int MAXM = 8;
+constexpr int TILE_N = 16;
+constexpr int TAIL_BYTES = TILE_N * 4;  // 16 x (bf16 scale, bf16 -(16+zero))
 
-template <int CW_, int SLOTS_, int TILE_ROWS_>
-struct Cfg {
-  static constexpr int CW = CW_;                // consumer warps
-  static constexpr int SLOTS = SLOTS_;          // ring slots per consumer warp
-  static constexpr int TILE_ROWS = TILE_ROWS_;  // packed rows per tile (k per tile = 2x)
-  static constexpr int TILE_K = 2 * TILE_ROWS_;
-  static constexpr int TILE_BYTES = TILE_ROWS_ * CHUNK;
-  static constexpr int SZ_BYTES = CHUNK * 4;
-  static constexpr int STEPS = TILE_ROWS_ / 8;
-  static constexpr int THREADS = (CW_ + 1) * 32;
-  static constexpr int NCONS = CW_ * 32;
-};
+__host__ __device__ inline int pick_kb(int K, int group) {
+  if (group <= 0 || K <= 0 || K % group != 0) return 0;
+  if (group % 128 == 0) return 128;
+  if (group % 64 == 0) return 64;
+  if (group % 32 == 0) return 32;
+  return 0;
+}
+__host__ __device__ inline int block_bytes(int kb) { return kb * 8 + TAIL_BYTES; }
 
 struct Params {
-  CUtensorMap map[2];
-  const uint32_t* sz[2];
-  int nmat;
-  int N, K, group, G;
-  int M;
+  const uint8_t* w[2];
+  int nmat, N, K, group, M;
+  int G;       // k-blocks per (tile, matrix) = K / KB
+  int GT;      // items per tile = nmat * G
+  int ntiles;  // N / 16
+  int I;       // total items
   const __nv_bfloat16* x;
   const __nv_bfloat16* norm_w;
   const float* ssq;
@@ -71,101 +68,105 @@ struct Params {
   int n_head, head_size, cache_len;
   float* partials;
   int32_t* counters;
-  int ksplit;
-  int nchunks, ktiles, tiles_per_split, nunits;
-  int xs_stride;  // elements per x row in smem (max slice length + 8)
+  int maxc;  // contributor slots per tile in `partials`
+  // shared-memory plan
+  int S;          // ring slots
+  int xs_stride;  // bytes per staged x row
+  int ts_max;     // (tile, matrix) slots of the cross-warp reduction
+  int off_xs, off_sx, off_red, off_cta, off_wv, off_bar;
 };
-
-struct Unit {
-  int mat, chunk, split, t0, t1;
-};
-
-__device__ __forceinline__ Unit decode_unit(const Params& p, int u) {
-  Unit r;
-  r.chunk = u % p.nchunks;
-  int rest = u / p.nchunks;
-  r.mat = rest % p.nmat;
-  r.split = rest / p.nmat;
-  r.t0 = r.split * p.tiles_per_split;
-  r.t1 = min(r.t0 + p.tiles_per_split, p.ktiles);
-  return r;
-}
 
 __device__ __forceinline__ void consumer_sync(int n) { asm volatile("bar.sync 1, %0;" ::"r"(n) : "memory"); }
 
-__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
-  uint32_t r;
-  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
-  return r;
-}
 __device__ __forceinline__ uint32_t lop_and_or(uint32_t a, uint32_t mask, uint32_t orv) {
   uint32_t r;
   asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(r) : "r"(a), "r"(mask), "r"(orv));  // (a & mask) | orv
   return r;
 }
-__device__ __forceinline__ uint32_t bf2_sub(uint32_t a, uint32_t b) {
+__device__ __forceinline__ uint32_t rotr(uint32_t a, uint32_t n) {
   uint32_t r;
-  asm("sub.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  asm("shf.r.wrap.b32 %0, %1, %1, %2;" : "=r"(r) : "r"(a), "r"(n));
   return r;
 }
-__device__ __forceinline__ uint32_t bf2_mul(uint32_t a, uint32_t b) {
-  uint32_t r;
-  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
-  return r;
+// 1-D bulk copy global -> shared with an L2 cache policy, completion on an mbarrier.
+__device__ __forceinline__ void bulk_load_1d_hint(void* dst, const void* src, uint32_t bytes, uint64_t* bar,
+                                                  uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+          smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
 }
 
-template <class C>
-__global__ void __launch_bounds__(C::THREADS, 2) gemv_int4_kernel(const __grid_constant__ Params p) {
-  extern __shared__ __align__(1024) uint8_t smem[];
-  // layout: [tiles CW*SLOTS*TILE_BYTES][sz CW*SLOTS*SZ_BYTES][x M*xs_stride*2][red CW*M*CHUNK*4 (also out)][barriers]
-  uint8_t* tiles = smem;
-  uint8_t* szs = tiles + C::CW * C::SLOTS * C::TILE_BYTES;
-  __nv_bfloat16* xs = reinterpret_cast<__nv_bfloat16*>(szs + C::CW * C::SLOTS * C::SZ_BYTES);
-  float* red = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(xs) + ((p.M * p.xs_stride * 2 + 15) & ~15));
-  float* outs = red + C::CW * p.M * CHUNK;           // [nmat][M][CHUNK] final sums
-  uint64_t* full = reinterpret_cast<uint64_t*>(outs + 2 * p.M * CHUNK);
-  uint64_t* empty = full + C::CW * C::SLOTS;
-  __shared__ int s_flag;
+// first item of CTA c when I items are split over P CTAs; owner(x) = the CTA holding item x
+__device__ __forceinline__ int range_start(int c, int I, int P) { return (int)(((long long)c * I) / P); }
+__device__ __forceinline__ int range_owner(int x, int I, int P) {
+  return (int)((((long long)(x + 1)) * P + I - 1) / I) - 1;
+}
+
+constexpr uint32_t NIB_MASK = 0x00780078u;   // nibble at bits 3..6 of each bf16 half
+constexpr uint32_t NIB_MAGIC = 0x41804180u;  // bf16 16.0: 16 + q exact for q in 0..15
+
+template <int W, int KSP>
+__global__ void __launch_bounds__((W + 1) * 32, (W >= 12) ? 2 : 1) gemv_int4_kernel(const __grid_constant__ Params p) {
+  constexpr int KB = 32 * KSP;
+  constexpr int BLK = KB * 8 + TAIL_BYTES;
+  constexpr int CH = W;  // items per chunk: one per consumer warp
+  constexpr int CHB = CH * BLK;
+  constexpr int NCONS = W * 32;
+  constexpr int LPB = KB / 8;  // lanes staging one k-block of x (8 elements each)
+
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* ring = smem;
+  uint8_t* xs = smem + p.off_xs;
+  float* sx = reinterpret_cast<float*>(smem + p.off_sx);    // [G][8]
+  float* red = reinterpret_cast<float*>(smem + p.off_red);  // [ts_max][W][M][16]
+  float* cta = reinterpret_cast<float*>(smem + p.off_cta);  // [ts_max][M][16]
+  float* wv = reinterpret_cast<float*>(smem + p.off_wv);    // [W][nmat][M][16]
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + p.off_bar);
+  uint64_t* empty = full + p.S;
   __shared__ float s_rnorm[MAXM];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int P = gridDim.x, c = blockIdx.x;
+  const int i0 = range_start(c, p.I, P), i1 = range_start(c + 1, p.I, P);
+  const int nch = (i1 - i0 + CH - 1) / CH;
+  const int G = p.G, S = p.S, M = p.M;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < C::CW * C::SLOTS; ++i) {
+    for (int i = 0; i < S; ++i) {
       mbar_init(&full[i], 1);
-      mbar_init(&empty[i], 1);
+      mbar_init(&empty[i], W);
     }
     fence_barrier_init();
   }
   __syncthreads();
   pdl_launch_dependents();
 
-  if (warp == C::CW) {
+  if (warp == W) {
     // =============================== producer warp ===============================
     if (lane == 0) {
-      prefetch_tensormap(&p.map[0]);
-      if (p.nmat > 1) prefetch_tensormap(&p.map[1]);
       const uint64_t pol = policy_evict_first();
-      uint32_t fill[C::CW];
-#pragma unroll
-      for (int w = 0; w < C::CW; ++w) fill[w] = 0;
-      for (int u = blockIdx.x; u < p.nunits; u += gridDim.x) {
-        const Unit un = decode_unit(p, u);
-        const int n0 = un.chunk * CHUNK;
-        const uint32_t sz_bytes = (uint32_t)min(CHUNK, p.N - n0) * 4u;
-        for (int t = un.t0; t < un.t1; ++t) {
-          const int w = (t - un.t0) % C::CW;
-          uint32_t cnt = 0;
-#pragma unroll
-          for (int ww = 0; ww < C::CW; ++ww)
-            if (ww == w) cnt = fill[ww]++;
-          const int slot = cnt % C::SLOTS;
-          const int idx = w * C::SLOTS + slot;
-          if (cnt >= (uint32_t)C::SLOTS) mbar_wait(&empty[idx], ((cnt / C::SLOTS) - 1) & 1);
-          mbar_expect_tx(&full[idx], C::TILE_BYTES + sz_bytes);
-          tma_load_2d(tiles + idx * C::TILE_BYTES, &p.map[un.mat], n0, t * C::TILE_ROWS, &full[idx], pol);
-          const int g = (t * C::TILE_K) / p.group;
-          bulk_load_1d(szs + idx * C::SZ_BYTES, p.sz[un.mat] + (size_t)g * p.N + n0, sz_bytes, &full[idx]);
+      int slot = 0;
+      uint32_t phase = 1;  // parity of the PREVIOUS use of the slot once the ring wraps
+      for (int ch = 0; ch < nch; ++ch, ++slot) {
+        if (slot == S) {
+          slot = 0;
+          phase ^= 1u;
+        }
+        if (ch >= S) mbar_wait(&empty[slot], phase);
+        const int a = i0 + ch * CH, b = min(a + CH, i1);
+        mbar_expect_tx(&full[slot], (uint32_t)(b - a) * BLK);
+        uint8_t* dst = ring + (size_t)slot * CHB;
+        int it = a;
+        while (it < b) {  // contiguous runs: a run ends where the (tile, matrix) changes
+          const int vt = it / G, g = it - vt * G;
+          const int run = min(G - g, b - it);
+          const int mat = p.nmat == 2 ? (vt & 1) : 0, tile = p.nmat == 2 ? (vt >> 1) : vt;
+          const uint8_t* src = p.w[mat] + ((size_t)tile * G + g) * BLK;
+          bulk_load_1d_hint(dst, src, (uint32_t)run * BLK, &full[slot], pol);
+          dst += (size_t)run * BLK;
+          it += run;
         }
       }
     }
@@ -175,349 +176,406 @@ __global__ void __launch_bounds__(C::THREADS, 2) gemv_int4_kernel(const __grid_c
   // ================================= consumer warps =================================
   const int g = lane >> 2, tig = lane & 3;
   const int ctid = threadIdx.x;  // 0..NCONS-1
+  const int vt_first = i0 / G, vt_last = (i1 - 1) / G;
+  const int nvt = vt_last - vt_first + 1;
+  const int MT = M * TILE_N;  // floats per (tile, matrix) result
+
+  for (int i = ctid; i < p.ts_max * W * MT; i += NCONS) red[i] = 0.f;
+  for (int i = ctid; i < G * 8; i += NCONS) sx[i] = 0.f;
+  consumer_sync(NCONS);
+
   pdl_wait();  // activations (x, ssq, residual, caches, scratch) come from earlier kernels
 
-  uint32_t consumed = 0;
-  int staged_t0 = -1, staged_t1 = -1;
-
-  for (int u = blockIdx.x; u < p.nunits; u += gridDim.x) {
-    const Unit un = decode_unit(p, u);
-    const int n0 = un.chunk * CHUNK;
-    const int kbeg = un.t0 * C::TILE_K;
-    const int klen = (un.t1 - un.t0) * C::TILE_K;
-
-    // ---- stage x[:, kbeg : kbeg+klen] as pre-permuted B fragments (x0,x2,x1,x3 per 4)
-    if (staged_t0 != un.t0 || staged_t1 != un.t1) {
-      consumer_sync(C::NCONS);  // previous unit's readers are done with xs
-      if (p.norm_w != nullptr) {
-        if (ctid < p.M) {
-          float s = 0.f;
-          for (int i = 0; i < p.ssq_parts; ++i) s += p.ssq[ctid * p.ssq_parts + i];
-          const float mean = bf16r(s * (1.0f / (float)p.K));
-          s_rnorm[ctid] = bf16r(rsqrtf(bf16r(mean + p.eps)));
-        }
-        consumer_sync(C::NCONS);
-      }
-      for (int m = 0; m < p.M; ++m) {
-        const float rn = p.norm_w != nullptr ? s_rnorm[m] : 0.f;
-        for (int q4 = ctid; q4 < klen / 4; q4 += C::NCONS) {
-          const int k = kbeg + q4 * 4;
-          uint16_t v[4];
-          if (k + 3 < p.K) {
-            const uint2 raw = *reinterpret_cast<const uint2*>(p.x + (size_t)m * p.K + k);
-            v[0] = raw.x & 0xffff; v[1] = raw.x >> 16; v[2] = raw.y & 0xffff; v[3] = raw.y >> 16;
-          } else {
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-              v[j] = (k + j < p.K) ? __bfloat16_as_ushort(p.x[(size_t)m * p.K + k + j]) : (uint16_t)0;
-          }
-          if (p.norm_w != nullptr) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              if (k + j < p.K) {
-                const float xn = bf16r(__fmul_rn(bf16_bits_to_f32(v[j]), rn));
-                v[j] = f32_to_bf16_bits(__fmul_rn(__bfloat162float(p.norm_w[k + j]), xn));
-              }
-            }
-          }
-          uint2 o;
-          o.x = (uint32_t)v[0] | ((uint32_t)v[2] << 16);
-          o.y = (uint32_t)v[1] | ((uint32_t)v[3] << 16);
-          *reinterpret_cast<uint2*>(xs + (size_t)m * p.xs_stride + q4 * 4) = o;
-        }
-      }
-      staged_t0 = un.t0; staged_t1 = un.t1;
-      consumer_sync(C::NCONS);
-    }
-
-    // ---- stream this warp's tiles
-    float acc[8][4];
-#pragma unroll
-    for (int i = 0; i < 8; ++i)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-
-    for (int t = un.t0 + warp; t < un.t1; t += C::CW) {
-      const int slot = consumed % C::SLOTS;
-      const int idx = warp * C::SLOTS + slot;
-      mbar_wait(&full[idx], (consumed / C::SLOTS) & 1);
-      const uint32_t tile = smem_u32(tiles + idx * C::TILE_BYTES);
-      const uint32_t szb = smem_u32(szs + idx * C::SZ_BYTES) + g * 64;
-      // scale / (128+zero) pairs for this thread's 16 columns, duplicated to both halves
-      uint32_t s2[16], z2[16];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const uint4 v = lds128(szb + q * 16);
-        s2[q * 4 + 0] = prmt(v.x, v.x, 0x1010); z2[q * 4 + 0] = prmt(v.x, v.x, 0x3232);
-        s2[q * 4 + 1] = prmt(v.y, v.y, 0x1010); z2[q * 4 + 1] = prmt(v.y, v.y, 0x3232);
-        s2[q * 4 + 2] = prmt(v.z, v.z, 0x1010); z2[q * 4 + 2] = prmt(v.z, v.z, 0x3232);
-        s2[q * 4 + 3] = prmt(v.w, v.w, 0x1010); z2[q * 4 + 3] = prmt(v.w, v.w, 0x3232);
-      }
-      const uint32_t xrow = smem_u32(xs) + (uint32_t)(((size_t)g * p.xs_stride + (size_t)(t - un.t0) * C::TILE_K + 4 * tig) * 2);
-#pragma unroll
-      for (int s = 0; s < C::STEPS; ++s) {
-        const int rA = 8 * s + 2 * tig, rB = rA + 1;
-        const uint4 A = lds128(tile + rA * CHUNK + ((g ^ (rA & 7)) << 4));
-        const uint4 B = lds128(tile + rB * CHUNK + ((g ^ (rB & 7)) << 4));
-        uint2 xb = make_uint2(0u, 0u);
-        if (g < p.M) xb = lds64(xrow + s * 32);
-        const uint32_t Aw[4] = {A.x, A.y, A.z, A.w};
-        const uint32_t Bw[4] = {B.x, B.y, B.z, B.w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            // bytes [A.b(2h), A.b(2h+1), B.b(2h), B.b(2h+1)]: columns 4j+2h and 4j+2h+1
-            const uint32_t uu = prmt(Aw[j], Bw[j], h == 0 ? 0x5410u : 0x7632u);
-            const int c0 = 4 * j + 2 * h, c1 = c0 + 1;
-            uint32_t a0 = lop_and_or(uu, 0x000f000fu, 0x43004300u);        // col c0, k (2rA, 2rB)
-            uint32_t a2 = lop_and_or(uu >> 4, 0x000f000fu, 0x43004300u);   // col c0, k (2rA+1, 2rB+1)
-            uint32_t a1 = lop_and_or(uu >> 8, 0x000f000fu, 0x43004300u);   // col c1, k (2rA, 2rB)
-            uint32_t a3 = lop_and_or(uu >> 12, 0x000f000fu, 0x43004300u);  // col c1, k (2rA+1, 2rB+1)
-            a0 = bf2_mul(bf2_sub(a0, z2[c0]), s2[c0]);
-            a2 = bf2_mul(bf2_sub(a2, z2[c0]), s2[c0]);
-            a1 = bf2_mul(bf2_sub(a1, z2[c1]), s2[c1]);
-            a3 = bf2_mul(bf2_sub(a3, z2[c1]), s2[c1]);
-            mma_bf16_16816(acc[2 * j + h], a0, a1, a2, a3, xb.x, xb.y);
-          }
-        }
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&empty[idx]);
-      ++consumed;
-    }
-
-    // ---- cross-warp reduction (fixed order).  acc[i]: c0,c1 -> column 16g+2i (batch 2tig, 2tig+1);
-    //      c2,c3 -> column 16g+2i+1.
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int ca = 16 * g + 2 * i, cb = ca + 1;
-      const int m0 = 2 * tig, m1 = m0 + 1;
-      if (m0 < p.M) {
-        red[(warp * p.M + m0) * CHUNK + ca] = acc[i][0];
-        red[(warp * p.M + m0) * CHUNK + cb] = acc[i][2];
-      }
-      if (m1 < p.M) {
-        red[(warp * p.M + m1) * CHUNK + ca] = acc[i][1];
-        red[(warp * p.M + m1) * CHUNK + cb] = acc[i][3];
+  // ---- stage x (natural order, optional fused RMSNorm) and its per-k-block sums
+  if (p.norm_w != nullptr) {
+    for (int m = warp; m < M; m += W) {
+      float s = 0.f;
+      for (int i = lane; i < p.ssq_parts; i += 32) s += p.ssq[m * p.ssq_parts + i];
+      s = warp_sum(s);
+      if (lane == 0) {
+        const float mean = bf16r(s * (1.0f / (float)p.K));
+        s_rnorm[m] = bf16r(rsqrtf(bf16r(mean + p.eps)));
       }
     }
-    consumer_sync(C::NCONS);
-    const int total = p.nmat * p.ksplit;
-    bool do_epilogue = true;
-    for (int e = ctid; e < p.M * CHUNK; e += C::NCONS) {
-      float v = 0.f;
+    consumer_sync(NCONS);
+  }
+  {
+    const int vpr = p.K >> 3, total = M * vpr;
+    for (int v0 = 0; v0 < total; v0 += NCONS) {
+      const int v = v0 + ctid;
+      const bool ok = v < total;
+      float part = 0.f;
+      int m = 0, k = 0;
+      if (ok) {
+        m = v / vpr;
+        k = (v - m * vpr) << 3;
+        uint4 raw = *reinterpret_cast<const uint4*>(p.x + (size_t)m * p.K + k);
+        uint32_t wd[4] = {raw.x, raw.y, raw.z, raw.w};
+        if (p.norm_w != nullptr) {
+          const float rn = s_rnorm[m];
+          const uint4 nraw = *reinterpret_cast<const uint4*>(p.norm_w + k);
+          const uint32_t nw[4] = {nraw.x, nraw.y, nraw.z, nraw.w};
 #pragma unroll
-      for (int w = 0; w < C::CW; ++w) v += red[w * p.M * CHUNK + e];
-      if (total > 1) {
-        const int m = e / CHUNK, c = e % CHUNK;
-        if (n0 + c < p.N)
-          p.partials[(((size_t)un.split * p.nmat + un.mat) * p.M + m) * p.N + n0 + c] = v;
-      } else {
-        outs[e] = v;
-      }
-    }
-    if (total > 1) {
-      __threadfence();
-      consumer_sync(C::NCONS);
-      if (ctid == 0) {
-        const int old = atomicAdd(&p.counters[un.chunk], 1);
-        s_flag = (old == total - 1);
-      }
-      consumer_sync(C::NCONS);
-      do_epilogue = s_flag != 0;
-      if (do_epilogue) {
-        __threadfence();
-        for (int e = ctid; e < p.nmat * p.M * CHUNK; e += C::NCONS) {
-          const int mat = e / (p.M * CHUNK), m = (e / CHUNK) % p.M, c = e % CHUNK;
-          float v = 0.f;
-          if (n0 + c < p.N)
-            for (int sp = 0; sp < p.ksplit; ++sp)
-              v += __ldcg(&p.partials[(((size_t)sp * p.nmat + mat) * p.M + m) * p.N + n0 + c]);
-          outs[e] = v;
-        }
-        if (ctid == 0) p.counters[un.chunk] = 0;
-      }
-    }
-    consumer_sync(C::NCONS);
-
-    // ---- fused epilogue on outs[mat][m][c]
-    if (do_epilogue) {
-      if (p.epilogue == LL_EPI_STORE) {
-        for (int e = ctid; e < p.M * CHUNK; e += C::NCONS) {
-          const int m = e / CHUNK, n = n0 + e % CHUNK;
-          if (n < p.N) {
-            float v = outs[e];
-            if (p.bias) v += __bfloat162float(p.bias[n]);
-            p.y[(size_t)m * p.N + n] = __float2bfloat16_rn(v);
+          for (int j = 0; j < 4; ++j) {
+            const float x0 = bf16r(__fmul_rn(bf16_bits_to_f32(wd[j] & 0xffffu), rn));
+            const float x1 = bf16r(__fmul_rn(bf16_bits_to_f32(wd[j] >> 16), rn));
+            const uint32_t o0 = f32_to_bf16_bits(__fmul_rn(bf16_bits_to_f32(nw[j] & 0xffffu), x0));
+            const uint32_t o1 = f32_to_bf16_bits(__fmul_rn(bf16_bits_to_f32(nw[j] >> 16), x1));
+            wd[j] = o0 | (o1 << 16);
           }
         }
-      } else if (p.epilogue == LL_EPI_RESIDUAL) {
-        // x = bf16(x + bf16(h)); partial sum of bf16(x*x) over this chunk for the next RMSNorm
-        for (int m = warp; m < p.M; m += C::CW) {
-          float ss = 0.f;
 #pragma unroll
-          for (int q = 0; q < CHUNK / 32; ++q) {
-            const int c = lane + 32 * q, n = n0 + c;
-            if (n < p.N) {
-              const float h = bf16r(outs[m * CHUNK + c]);
-              const float xn = bf16r(__fadd_rn(__bfloat162float(p.y[(size_t)m * p.N + n]), h));
-              p.y[(size_t)m * p.N + n] = __float2bfloat16_rn(xn);
-              ss += bf16r(__fmul_rn(xn, xn));
-            }
-          }
-          ss = warp_sum(ss);
-          if (lane == 0 && p.ssq_out) p.ssq_out[m * p.nchunks + un.chunk] = ss;
-        }
-      } else if (p.epilogue == LL_EPI_ROPE_KV) {
-        const int E = p.N / 3, hs = p.head_size;
-        const int rope_pos = p.pos[0], slot = p.pos[1];
-        for (int e = ctid; e < p.M * (CHUNK / 2); e += C::NCONS) {
-          const int m = e / (CHUNK / 2), c = 2 * (e % (CHUNK / 2)), n = n0 + c;
-          if (n < p.N) {
-            const int part = n / E, ee = n % E, head = ee / hs, d = ee % hs;
-            float x0 = bf16r(outs[m * CHUNK + c]), x1 = bf16r(outs[m * CHUNK + c + 1]);
-            if (part < 2) {
-              const float2 cs = *reinterpret_cast<const float2*>(p.rope + ((size_t)rope_pos * (hs / 2) + d / 2) * 2);
-              const float o0 = __fsub_rn(__fmul_rn(x0, cs.x), __fmul_rn(x1, cs.y));
-              const float o1 = __fadd_rn(__fmul_rn(x1, cs.x), __fmul_rn(x0, cs.y));
-              x0 = o0; x1 = o1;
-            }
-            const __nv_bfloat162 o = __floats2bfloat162_rn(x0, x1);
-            if (part == 0) {
-              *reinterpret_cast<__nv_bfloat162*>(p.y + (size_t)m * E + ee) = o;
-            } else {
-              __nv_bfloat16* cache = part == 1 ? p.k_cache : p.v_cache;
-              *reinterpret_cast<__nv_bfloat162*>(cache + (((size_t)m * p.n_head + head) * p.cache_len + slot) * hs + d) = o;
-            }
-          }
-        }
-      } else {  // LL_EPI_SWIGLU
-        for (int e = ctid; e < p.M * CHUNK; e += C::NCONS) {
-          const int m = e / CHUNK, n = n0 + e % CHUNK;
-          if (n < p.N) {
-            const float a = bf16r(outs[e]), b = bf16r(outs[p.M * CHUNK + e]);
-            const float s = bf16r(a / (1.0f + expf(-a)));
-            p.y[(size_t)m * p.N + n] = __float2bfloat16_rn(__fmul_rn(s, b));
-          }
-        }
+        for (int j = 0; j < 4; ++j) part += bf16_bits_to_f32(wd[j] & 0xffffu) + bf16_bits_to_f32(wd[j] >> 16);
+        *reinterpret_cast<uint4*>(xs + (size_t)m * p.xs_stride + k * 2) = make_uint4(wd[0], wd[1], wd[2], wd[3]);
       }
+#pragma unroll
+      for (int o = LPB / 2; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+      if (ok && (lane % LPB) == 0) sx[(k / KB) * 8 + m] = part;
     }
   }
+  consumer_sync(NCONS);
+
+  // ---- stream this CTA's items
+  float out[4] = {0.f, 0.f, 0.f, 0.f};
+  int cur_vt = -1;
+  const uint32_t xs_lane = smem_u32(xs) + (uint32_t)(g * p.xs_stride + tig * 16);
+  const uint32_t sx_lane = smem_u32(sx) + (uint32_t)(tig * 8);
+  const bool has_x = g < M;
+
+  auto flush = [&](int vt) {
+    float* r = red + ((size_t)(vt - vt_first) * W + warp) * MT;
+    const int m0 = 2 * tig, m1 = m0 + 1;
+    if (m0 < M) {
+      r[m0 * TILE_N + g] = out[0];
+      r[m0 * TILE_N + g + 8] = out[2];
+    }
+    if (m1 < M) {
+      r[m1 * TILE_N + g] = out[1];
+      r[m1 * TILE_N + g + 8] = out[3];
+    }
+  };
+
+  int it = i0 + warp, vt = 0, gk = 0;
+  if (it < i1) {
+    vt = it / G;
+    gk = it - vt * G;
+  }
+  int slot = 0;
+  uint32_t phase = 0;
+  for (int ch = 0; ch < nch; ++ch) {
+    mbar_wait(&full[slot], phase);
+    if (it < i1) {
+      if (vt != cur_vt) {
+        if (cur_vt >= 0) flush(cur_vt);
+        cur_vt = vt;
+        out[0] = out[1] = out[2] = out[3] = 0.f;
+      }
+      const uint32_t blk = smem_u32(ring) + (uint32_t)(slot * CHB + warp * BLK);
+      const uint2 sz = lds64(blk + KB * 8 + g * 8);
+      const uint2 sxv = lds64(sx_lane + gk * 32);
+      const float s0 = __uint_as_float(sz.x << 16), zn0 = __uint_as_float(sz.x & 0xffff0000u);
+      const float s1 = __uint_as_float(sz.y << 16), zn1 = __uint_as_float(sz.y & 0xffff0000u);
+      const float sx0 = __uint_as_float(sxv.x), sx1 = __uint_as_float(sxv.y);
+      float accA[4] = {zn0 * sx0, zn0 * sx1, zn1 * sx0, zn1 * sx1};
+      float accB[4] = {0.f, 0.f, 0.f, 0.f};
+      const uint32_t xk = xs_lane + (uint32_t)(gk * KB * 2);
+      auto step_pair = [&](uint32_t w0, uint32_t w1, int sp) {
+        uint4 xv = make_uint4(0u, 0u, 0u, 0u);
+        if (has_x) xv = lds128(xk + sp * 64);
+        {
+          const uint32_t a0 = lop_and_or(w0, NIB_MASK, NIB_MAGIC);
+          const uint32_t a1 = lop_and_or(w0 >> 4, NIB_MASK, NIB_MAGIC);
+          const uint32_t a2 = lop_and_or(w0 >> 8, NIB_MASK, NIB_MAGIC);
+          const uint32_t a3 = lop_and_or(rotr(w0, 12), NIB_MASK, NIB_MAGIC);
+          mma_bf16_16816(accA, a0, a1, a2, a3, xv.x, xv.y);
+        }
+        {
+          const uint32_t a0 = lop_and_or(w1, NIB_MASK, NIB_MAGIC);
+          const uint32_t a1 = lop_and_or(w1 >> 4, NIB_MASK, NIB_MAGIC);
+          const uint32_t a2 = lop_and_or(w1 >> 8, NIB_MASK, NIB_MAGIC);
+          const uint32_t a3 = lop_and_or(rotr(w1, 12), NIB_MASK, NIB_MAGIC);
+          mma_bf16_16816(accB, a0, a1, a2, a3, xv.z, xv.w);
+        }
+      };
+      if constexpr (KSP == 1) {
+        const uint2 t = lds64(blk + lane * 8);
+        step_pair(t.x, t.y, 0);
+      } else {
+#pragma unroll
+        for (int h = 0; h < KSP / 2; ++h) {
+          const uint4 t = lds128(blk + h * 512 + lane * 16);
+          step_pair(t.x, t.y, 2 * h);
+          step_pair(t.z, t.w, 2 * h + 1);
+        }
+      }
+      out[0] = fmaf(s0, accA[0] + accB[0], out[0]);
+      out[1] = fmaf(s0, accA[1] + accB[1], out[1]);
+      out[2] = fmaf(s1, accA[2] + accB[2], out[2]);
+      out[3] = fmaf(s1, accA[3] + accB[3], out[3]);
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[slot]);
+    it += CH;
+    gk += CH;
+    while (gk >= G) {
+      gk -= G;
+      ++vt;
+    }
+    if (++slot == S) {
+      slot = 0;
+      phase ^= 1u;
+    }
+  }
+  if (cur_vt >= 0) flush(cur_vt);
+  consumer_sync(NCONS);
+
+  // ---- cross-warp reduction (fixed warp order) into cta[slot][m][n]
+  for (int e = ctid; e < nvt * MT; e += NCONS) {
+    const int sv = e / MT, r = e - sv * MT;
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < W; ++w) v += red[((size_t)sv * W + w) * MT + r];
+    cta[e] = v;
+  }
+  consumer_sync(NCONS);
+
+  // ---- per tile: (cross-CTA combine) + fused epilogue, one warp per tile
+  const int nmat = p.nmat, GT = p.GT;
+  const int T_first = vt_first / nmat, T_last = vt_last / nmat;
+  float* vals = wv + (size_t)warp * nmat * MT;  // [nmat][M][16]
+  for (int T = T_first + warp; T <= T_last; T += W) {
+    const int c_lo = range_owner(T * GT, p.I, P), c_hi = range_owner((T + 1) * GT - 1, p.I, P);
+    const int ncontrib = c_hi - c_lo + 1;
+    // this CTA's (possibly partial) sums for the tile; zero where it holds no item of a matrix
+    for (int e = lane; e < nmat * MT; e += 32) {
+      const int mat = e / MT, r = e - mat * MT;
+      const int vt = T * nmat + mat;
+      vals[e] = (vt >= vt_first && vt <= vt_last) ? cta[(size_t)(vt - vt_first) * MT + r] : 0.f;
+    }
+    __syncwarp();
+    bool run_epilogue = true;
+    if (ncontrib > 1) {
+      float* mine = p.partials + ((size_t)T * p.maxc + (c - c_lo)) * nmat * MT;
+      for (int e = lane; e < nmat * MT; e += 32) mine[e] = vals[e];
+      __threadfence();
+      __syncwarp();
+      int last = 0;
+      if (lane == 0) {
+        last = (atomicAdd(&p.counters[T], 1) == ncontrib - 1);
+        if (last) __threadfence();
+      }
+      last = __shfl_sync(0xffffffffu, last, 0);
+      run_epilogue = last != 0;
+      if (run_epilogue) {
+        const float* base = p.partials + (size_t)T * p.maxc * nmat * MT;
+        for (int e = lane; e < nmat * MT; e += 32) {
+          float v = 0.f;
+          for (int i = 0; i < ncontrib; ++i) v += __ldcg(base + (size_t)i * nmat * MT + e);
+          vals[e] = v;
+        }
+        if (lane == 0) p.counters[T] = 0;
+        __syncwarp();
+      }
+    }
+    if (!run_epilogue) continue;
+
+    const int n0 = T * TILE_N;
+    if (p.epilogue == LL_EPI_STORE) {
+      for (int e = lane; e < MT; e += 32) {
+        const int m = e >> 4, n = n0 + (e & 15);
+        float v = vals[e];
+        if (p.bias) v += __bfloat162float(p.bias[n]);
+        p.y[(size_t)m * p.N + n] = __float2bfloat16_rn(v);
+      }
+    } else if (p.epilogue == LL_EPI_RESIDUAL) {
+      // x = bf16(x + bf16(h)); partial sum of bf16(x*x) over this tile for the next RMSNorm
+      for (int mm = 0; mm < M; mm += 2) {
+        const int m = mm + (lane >> 4), nl = lane & 15;
+        float ss = 0.f;
+        if (m < M) {
+          const size_t o = (size_t)m * p.N + n0 + nl;
+          const float h = bf16r(vals[m * TILE_N + nl]);
+          const float xn = bf16r(__fadd_rn(__bfloat162float(p.y[o]), h));
+          p.y[o] = __float2bfloat16_rn(xn);
+          ss = bf16r(__fmul_rn(xn, xn));
+        }
+        ss += __shfl_xor_sync(0xffffffffu, ss, 8);
+        ss += __shfl_xor_sync(0xffffffffu, ss, 4);
+        ss += __shfl_xor_sync(0xffffffffu, ss, 2);
+        ss += __shfl_xor_sync(0xffffffffu, ss, 1);
+        if (m < M && nl == 0 && p.ssq_out) p.ssq_out[(size_t)m * p.ntiles + T] = ss;
+      }
+    } else if (p.epilogue == LL_EPI_ROPE_KV) {
+      const int E = p.N / 3, hs = p.head_size;
+      const int rope_pos = p.pos[0], slot = p.pos[1];
+      for (int e = lane; e < M * (TILE_N / 2); e += 32) {
+        const int m = e >> 3, cc = 2 * (e & 7), n = n0 + cc;
+        const int part = n / E, ee = n - part * E, head = ee / hs, d = ee - head * hs;
+        float x0 = bf16r(vals[m * TILE_N + cc]), x1 = bf16r(vals[m * TILE_N + cc + 1]);
+        if (part < 2) {
+          const float2 cs = *reinterpret_cast<const float2*>(p.rope + ((size_t)rope_pos * (hs / 2) + d / 2) * 2);
+          const float o0 = __fsub_rn(__fmul_rn(x0, cs.x), __fmul_rn(x1, cs.y));
+          const float o1 = __fadd_rn(__fmul_rn(x1, cs.x), __fmul_rn(x0, cs.y));
+          x0 = o0; x1 = o1;
+        }
+        const __nv_bfloat162 o = __floats2bfloat162_rn(x0, x1);
+        if (part == 0) {
+          *reinterpret_cast<__nv_bfloat162*>(p.y + (size_t)m * E + ee) = o;
+        } else {
+          __nv_bfloat16* cache = part == 1 ? p.k_cache : p.v_cache;
+          *reinterpret_cast<__nv_bfloat162*>(cache + (((size_t)m * p.n_head + head) * p.cache_len + slot) * hs + d) = o;
+        }
+      }
+    } else {  // LL_EPI_SWIGLU
+      for (int e = lane; e < MT; e += 32) {
+        const int m = e >> 4, n = n0 + (e & 15);
+        const float a = bf16r(vals[e]), b = bf16r(vals[MT + e]);
+        const float sl = bf16r(a / (1.0f + expf(-a)));
+        p.y[(size_t)m * p.N + n] = __float2bfloat16_rn(__fmul_rn(sl, b));
+      }
+    }
+    __syncwarp();
+  }
 }
+
+// ------------------------------------------------------------------------------------ repack
+// One thread per 32-bit fragment word (and per tail entry).  ref layout: quantization.py:349-357, 385-388.
+template <typename P>
+__global__ void int4_repack_kernel(const uint8_t* __restrict__ qw, const P* __restrict__ scales, const P* __restrict__ zeros,
+                                   uint8_t* __restrict__ out, int N, int K, int group, int KB, int32_t* status) {
+  const int G = K / KB, Gq = K / group;
+  const int BLK = block_bytes(KB);
+  const int words = KB * 2;          // fragment words per block
+  const int per_blk = words + TILE_N;  // + tail entries
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long nblk = (long long)(N / TILE_N) * G;
+  if (idx >= nblk * per_blk) return;
+  const long long b = idx / per_blk;
+  const int r = (int)(idx - b * per_blk);
+  const int tile = (int)(b / G), gk = (int)(b - (long long)tile * G);
+  uint8_t* blk = out + (size_t)b * BLK;
+  if (r >= words) {  // tail: entry e -> column tile*16 + (e>>1) + 8*(e&1)
+    const int e = r - words;
+    const int n = tile * TILE_N + (e >> 1) + 8 * (e & 1);
+    const int gq = (gk * KB) / group;
+    const float s = dt<P>::ld(scales, (size_t)n * Gq + gq);
+    const float z = dt<P>::ld(zeros, (size_t)n * Gq + gq);
+    const float zn = -(16.f + z);
+    if (!(bf16r(zn) == zn) || !(bf16r(s) == s)) atomicExch(status, 1);
+    reinterpret_cast<uint32_t*>(blk + KB * 8)[e] = (uint32_t)f32_to_bf16_bits(s) | ((uint32_t)f32_to_bf16_bits(zn) << 16);
+    return;
+  }
+  // word r: lane, step pair, which half of the pair
+  int lane, sp, e0;
+  if (KB == 32) {
+    lane = r >> 1; sp = 0; e0 = (r & 1) * 4;
+  } else {
+    const int h = r >> 7, rr = r & 127;  // 128 words (512 B) per LDS.128 row of the warp
+    lane = rr >> 2;
+    const int j = rr & 3;
+    sp = 2 * h + (j >> 1);
+    e0 = (j & 1) * 4;
+  }
+  const int g = lane >> 2, tig = lane & 3;
+  const int kbase = gk * KB + sp * 32 + tig * 8 + e0;
+  const int n_lo = tile * TILE_N + g, n_hi = n_lo + 8;
+  auto nib = [&](int n, int k) -> uint32_t { return (qw[(size_t)(k >> 1) * N + n] >> ((k & 1) * 4)) & 15u; };
+  auto rotl = [](uint32_t v, int s) -> uint32_t { return (v << s) | (v >> (32 - s)); };
+  uint32_t w = 0;
+  w |= rotl(nib(n_lo, kbase + 0), 3) | rotl(nib(n_lo, kbase + 1), 19);
+  w |= rotl(nib(n_hi, kbase + 0), 7) | rotl(nib(n_hi, kbase + 1), 23);
+  w |= rotl(nib(n_lo, kbase + 2), 11) | rotl(nib(n_lo, kbase + 3), 27);
+  w |= rotl(nib(n_hi, kbase + 2), 15) | rotl(nib(n_hi, kbase + 3), 31);
+  const int off = (KB == 32) ? r * 4 : ((r >> 7) * 512 + (r & 127) * 4);
+  *reinterpret_cast<uint32_t*>(blk + off) = w;
+}
+
 
 // ------------------------------------------------------------------------------------ host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
-        qres == cudaDriverEntryPointSuccess)
-      fn = (EncodeTiledFn)p;
-  });
-  return fn;
-}
-
-struct MapKey {
-  const void* ptr;
-  int N, rows, tile_rows;
-  bool operator==(const MapKey& o) const { return ptr == o.ptr && N == o.N && rows == o.rows && tile_rows == o.tile_rows; }
-};
-struct MapKeyHash {
-  size_t operator()(const MapKey& k) const {
-    return std::hash<const void*>()(k.ptr) ^ (size_t)k.N * 1000003u ^ (size_t)k.rows * 10007u ^ (size_t)k.tile_rows;
-  }
+struct Plan {
+  int KB, KSP, BLK, W;
+  int G, GT, ntiles, I, P;
+  int maxc, ts_max, S;
+  int xs_stride, off_xs, off_sx, off_red, off_cta, off_wv, off_bar;
+  size_t smem;
 };
 
-int get_map(const uint8_t* qw, int N, int rows, int tile_rows, CUtensorMap* out) {
-  static std::mutex mu;
-  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
-  MapKey key{qw, N, rows, tile_rows};
-  std::lock_guard<std::mutex> lk(mu);
-  auto it = cache.find(key);
-  if (it != cache.end()) {
-    *out = it->second;
-    return LL_OK;
-  }
-  EncodeTiledFn fn = encode_fn();
-  if (!fn) {
-    set_error("cuTensorMapEncodeTiled entry point not available");
-    return LL_ERR_CUDA;
-  }
-  cuuint64_t dims[2] = {(cuuint64_t)N, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)N};
-  cuuint32_t box[2] = {(cuuint32_t)CHUNK, (cuuint32_t)tile_rows};
-  cuuint32_t estr[2] = {1, 1};
-  CUtensorMap m;
-  CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void*)qw, dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    set_error("cuTensorMapEncodeTiled failed (%d) for qw=%p N=%d rows=%d", (int)r, (const void*)qw, N, rows);
-    return LL_ERR_CUDA;
-  }
-  if (cache.size() > 4096) cache.clear();
-  cache.emplace(key, m);
-  *out = m;
-  return LL_OK;
-}
+constexpr int SMEM_CORESIDENT = 110 * 1024;  // two such CTAs (this GEMV + the next one, under PDL) fit one SM
+constexpr int SMEM_SOLO = 220 * 1024;
+constexpr int MAX_SLOTS = 12;
 
-int pick_tile_rows(int group) {
-  if (group % 128 == 0) return 64;
-  if (group % 64 == 0) return 32;
-  if (group % 32 == 0) return 16;
-  return 0;
-}
+int consumer_warps(int M) { return M <= 2 ? 12 : (M <= 4 ? 8 : 4); }
 
-constexpr int MAX_KSPLIT = 32;
-constexpr int XS_BUDGET = 24 * 1024;  // bytes of shared memory for staged x per CTA
-
-// K split: fill ~2 CTAs per SM, keep the staged x slice within budget, minimise the makespan.
-int choose_ksplit(int N, int K, int group, int nmat, int M, int tile_rows, int sms) {
-  const int nchunks = (N + CHUNK - 1) / CHUNK;
-  const int ktiles = (K / 2 + tile_rows - 1) / tile_rows;
-  const int slots = sms * 2;
-  const int tile_k = 2 * tile_rows;
-  int min_split = 1;
-  while ((long)((ktiles + min_split - 1) / min_split) * tile_k * M * 2 > XS_BUDGET && min_split < ktiles) ++min_split;
-  int best = min_split;
-  double best_cost = 1e30;
-  for (int ks = min_split; ks <= ktiles && ks <= MAX_KSPLIT; ++ks) {
-    const int tps = (ktiles + ks - 1) / ks;
-    const int ks_eff = (ktiles + tps - 1) / tps;
-    if (ks_eff != ks) continue;
-    const long units = (long)nchunks * nmat * ks;
-    const long waves = (units + slots - 1) / slots;
-    // per unit: tiles handled 4 warps wide + fixed cost (stage x, reduce, epilogue, split-K fixup)
-    const double per_unit = (double)((tps + 3) / 4) * (tile_rows / 64.0) + 0.75 + (ks > 1 ? 0.25 : 0.0);
-    const double cost = waves * per_unit;
-    if (cost < best_cost - 1e-9) {
-      best_cost = cost;
-      best = ks;
-    }
-  }
-  return best;
-}
-
-template <class C>
-int launch_cfg(Params& p, const ll_gemv_args* a, cudaStream_t st) {
-  const size_t smem = (size_t)C::CW * C::SLOTS * (C::TILE_BYTES + C::SZ_BYTES) + ((p.M * p.xs_stride * 2 + 15) & ~15) +
-                      (size_t)(C::CW + 2) * p.M * CHUNK * 4 + (size_t)2 * C::CW * C::SLOTS * 8;
-  static size_t configured = 0;
-  if (smem > configured) {
-    LL_CUDA(cudaFuncSetAttribute(gemv_int4_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
+// Fills `pl`; returns LL_OK, or LL_ERR_UNSUPPORTED with a message when the shape does not fit.
+int make_plan(int N, int K, int group, int nmat, int M, int grid, Plan* pl) {
+  const int KB = pick_kb(K, group);
+  if (KB == 0 || N % TILE_N != 0 || K % 8 != 0) {
+    set_error("int4 GEMV needs N %% 16 == 0, K %% group == 0 and group %% 32 == 0 (N=%d K=%d group=%d)", N, K, group);
+    return LL_ERR_UNSUPPORTED;
   }
   const int sms = sm_count();
-  const int grid = p.nunits < 2 * sms ? p.nunits : 2 * sms;
-  LL_CUDA(launch(gemv_int4_kernel<C>, dim3(grid), dim3(C::THREADS), smem, st, (a->flags & LL_GEMV_PDL) != 0, p));
+  if (sms <= 0) {
+    set_error("no CUDA device");
+    return LL_ERR_CUDA;
+  }
+  Plan& q = *pl;
+  q.KB = KB; q.KSP = KB / 32; q.BLK = block_bytes(KB); q.W = consumer_warps(M);
+  q.G = K / KB; q.GT = nmat * q.G; q.ntiles = N / TILE_N;
+  const long long items = (long long)q.ntiles * q.GT;
+  if (items > 0x3fffffff) {
+    set_error("int4 GEMV: too many work items (%lld)", items);
+    return LL_ERR_UNSUPPORTED;
+  }
+  q.I = (int)items;
+  q.P = grid > 0 ? grid : sms;
+  if (q.P > q.I) q.P = q.I;
+  const int ipc_min = q.I / q.P, ipc_max = (q.I + q.P - 1) / q.P;
+  q.maxc = (q.GT + ipc_min - 1) / ipc_min + 1;
+  q.ts_max = (ipc_max + q.G - 2) / q.G + 2;
+  const int MT = M * TILE_N;
+  q.xs_stride = K * 2 + 64;
+  size_t fixed = 0;
+  auto take = [&](size_t bytes) { size_t o = fixed; fixed += (bytes + 127) & ~(size_t)127; return (int)o; };
+  q.off_xs = take((size_t)M * q.xs_stride);
+  q.off_sx = take((size_t)q.G * 8 * 4);
+  q.off_red = take((size_t)q.ts_max * q.W * MT * 4);
+  q.off_cta = take((size_t)q.ts_max * MT * 4);
+  q.off_wv = take((size_t)q.W * nmat * MT * 4);
+  q.off_bar = take((size_t)2 * MAX_SLOTS * 8);
+  const size_t chb = (size_t)q.W * q.BLK;
+  const int nch_max = (ipc_max + q.W - 1) / q.W;
+  long s = ((long)SMEM_CORESIDENT - (long)fixed) / (long)chb;
+  if (s < 3 && nch_max > s) s = ((long)SMEM_SOLO - (long)fixed) / (long)chb;
+  if (s > MAX_SLOTS) s = MAX_SLOTS;
+  if (s > nch_max) s = nch_max;
+  if (s < 1 || (s < 2 && nch_max > 1)) {
+    set_error("int4 GEMV: M*K too large for shared memory (M=%d K=%d); use ll_qlinear_simt", M, K);
+    return LL_ERR_UNSUPPORTED;
+  }
+  q.S = (int)s;
+  const size_t ring = (size_t)q.S * chb;
+  q.off_xs += (int)ring; q.off_sx += (int)ring; q.off_red += (int)ring; q.off_cta += (int)ring;
+  q.off_wv += (int)ring; q.off_bar += (int)ring;
+  q.smem = ring + fixed;
   return LL_OK;
+}
+
+template <int W, int KSP>
+int launch_cfg(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
+  static size_t configured = 0;
+  if (pl.smem > configured) {
+    LL_CUDA(cudaFuncSetAttribute(gemv_int4_kernel<W, KSP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+    configured = pl.smem;
+  }
+  LL_CUDA(launch(gemv_int4_kernel<W, KSP>, dim3(pl.P), dim3((W + 1) * 32), pl.smem, st, pdl, p));
+  return LL_OK;
+}
+
+template <int W>
+int launch_w(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
+  if (pl.KSP == 4) return launch_cfg<W, 4>(p, pl, pdl, st);
+  if (pl.KSP == 2) return launch_cfg<W, 2>(p, pl, pdl, st);
+  return launch_cfg<W, 1>(p, pl, pdl, st);
 }
 
 }  // namespace
@@ -527,55 +585,72 @@ using namespace llb;
 
 extern "C" {
 
-int ll_int4_gemv_plan(int N, int K, int group, int nmat, int M, int32_t* ksplit, size_t* partial_bytes,
-                      size_t* counter_bytes) {
-  LL_CHECK_ARG(N > 0 && K > 0 && group > 0 && (nmat == 1 || nmat == 2) && M >= 1 && M <= MAXM, "bad plan arguments");
-  const int tr = pick_tile_rows(group);
-  LL_CHECK_ARG(tr != 0, "group size %d is not a multiple of 32", group);
-  const int sms = sm_count();
-  if (sms < 0) {
-    set_error("no CUDA device");
-    return LL_ERR_CUDA;
+size_t ll_int4_stream_bytes(int N, int K, int group) {
+  const int KB = pick_kb(K, group);
+  if (KB == 0 || N <= 0 || N % TILE_N != 0 || K % 8 != 0) return 0;
+  return (size_t)(N / TILE_N) * (K / KB) * block_bytes(KB);
+}
+
+int ll_int4_prepare(const uint8_t* qw, const void* scales, const void* zeros, int pdt, uint8_t* out, int N, int K,
+                    int group, int32_t* status, ll_stream stream) {
+  LL_CHECK_ARG(qw && scales && zeros && out && status, "null pointer");
+  const int KB = pick_kb(K, group);
+  if (KB == 0 || N <= 0 || N % TILE_N != 0 || K % 8 != 0) {
+    set_error("int4_prepare: unsupported shape N=%d K=%d group=%d", N, K, group);
+    return LL_ERR_UNSUPPORTED;
   }
-  const int ks = choose_ksplit(N, K, group, nmat, M, tr, sms);
-  if (ksplit) *ksplit = ks;
-  if (partial_bytes) *partial_bytes = (size_t)ks * nmat * M * N * sizeof(float);
-  if (counter_bytes) *counter_bytes = (size_t)((N + CHUNK - 1) / CHUNK) * sizeof(int32_t);
+  LL_CHECK_ARG(((uintptr_t)out & 15) == 0, "stream buffer must be 16-byte aligned");
+  const long long nblk = (long long)(N / TILE_N) * (K / KB);
+  const long long total = nblk * (KB * 2 + TILE_N);
+  const unsigned blocks = (unsigned)((total + 255) / 256);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (pdt == LL_F32) int4_repack_kernel<float><<<blocks, 256, 0, st>>>(qw, (const float*)scales, (const float*)zeros, out, N, K, group, KB, status);
+  else if (pdt == LL_BF16) int4_repack_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(qw, (const __nv_bfloat16*)scales, (const __nv_bfloat16*)zeros, out, N, K, group, KB, status);
+  else {
+    set_error("int4_prepare: unsupported param dtype %d", pdt);
+    return LL_ERR_UNSUPPORTED;
+  }
+  LL_LAUNCH_OK("int4_repack_kernel");
+  return LL_OK;
+}
+
+int ll_int4_gemv_plan(int N, int K, int group, int nmat, int M, int grid, size_t* partial_bytes, size_t* counter_bytes) {
+  LL_CHECK_ARG(N > 0 && K > 0 && group > 0 && (nmat == 1 || nmat == 2) && M >= 1 && M <= MAXM, "bad plan arguments");
+  Plan pl;
+  if (int r = make_plan(N, K, group, nmat, M, grid, &pl)) return r;
+  if (partial_bytes) *partial_bytes = (size_t)pl.ntiles * pl.maxc * nmat * M * TILE_N * sizeof(float);
+  if (counter_bytes) *counter_bytes = (size_t)pl.ntiles * sizeof(int32_t);
   return LL_OK;
 }
 
 int ll_int4_gemv(const ll_gemv_args* a, ll_stream stream) {
   LL_CHECK_ARG(a != nullptr, "null args");
-  LL_CHECK_ARG(a->qw && a->sz && a->x && a->y, "null pointer in gemv args");
+  LL_CHECK_ARG(a->w && a->x && a->y, "null pointer in gemv args");
   LL_CHECK_ARG(a->M >= 1 && a->M <= MAXM, "M must be in 1..8 (got %d)", a->M);
-  LL_CHECK_ARG(a->N > 0 && a->N % 16 == 0, "N must be a positive multiple of 16 (got %d)", a->N);
-  LL_CHECK_ARG(a->K > 0 && a->K % 8 == 0, "K must be a positive multiple of 8 (got %d)", a->K);
-  LL_CHECK_ARG(a->group > 0 && (a->group == a->K || a->K % a->group == 0 || true), "bad group");
-  const int tr = pick_tile_rows(a->group);
-  LL_CHECK_ARG(tr != 0, "group size %d is not a multiple of 32", a->group);
-  LL_CHECK_ARG(((uintptr_t)a->qw & 15) == 0 && ((uintptr_t)a->sz & 15) == 0 && ((uintptr_t)a->x & 7) == 0,
-               "qw/sz must be 16-byte aligned, x 8-byte aligned");
+  LL_CHECK_ARG(a->N > 0 && a->K > 0 && a->group > 0, "bad shape N=%d K=%d group=%d", a->N, a->K, a->group);
+  LL_CHECK_ARG(a->epilogue >= 0 && a->epilogue <= 3, "bad epilogue %d", a->epilogue);
   const int nmat = a->epilogue == LL_EPI_SWIGLU ? 2 : 1;
-  if (nmat == 2) LL_CHECK_ARG(a->qw2 && a->sz2, "SWIGLU epilogue needs qw2/sz2");
-  if (a->norm_weight) LL_CHECK_ARG(a->ssq && a->ssq_parts > 0, "fused RMSNorm needs ssq partials");
+  if (nmat == 2) LL_CHECK_ARG(a->w2 != nullptr, "SWIGLU epilogue needs w2");
+  LL_CHECK_ARG(((uintptr_t)a->w & 15) == 0 && ((uintptr_t)a->w2 & 15) == 0 && ((uintptr_t)a->x & 15) == 0,
+               "w/w2/x must be 16-byte aligned");
+  if (a->norm_weight) {
+    LL_CHECK_ARG(a->ssq && a->ssq_parts > 0, "fused RMSNorm needs ssq partials");
+    LL_CHECK_ARG(((uintptr_t)a->norm_weight & 15) == 0, "norm_weight must be 16-byte aligned");
+  }
   if (a->epilogue == LL_EPI_ROPE_KV) {
     LL_CHECK_ARG(a->rope && a->pos && a->k_cache && a->v_cache, "ROPE_KV epilogue needs rope/pos/caches");
     LL_CHECK_ARG(a->N % 3 == 0 && (a->N / 3) % 2 == 0 && a->head_size % 2 == 0 && a->n_head * a->head_size == a->N / 3,
                  "ROPE_KV: N must be 3*n_head*head_size");
   }
-  LL_CHECK_ARG(a->epilogue >= 0 && a->epilogue <= 3, "bad epilogue %d", a->epilogue);
+  Plan pl;
+  if (int r = make_plan(a->N, a->K, a->group, nmat, a->M, a->grid, &pl)) return r;
+  if (pl.maxc > 0 && pl.P > 1) LL_CHECK_ARG(a->partials && a->counters, "multi-CTA launch needs partials and counters scratch");
 
   Params p;
   memset(&p, 0, sizeof(p));
-  const int rows = a->K / 2;
-  if (int r = get_map(a->qw, a->N, rows, tr, &p.map[0])) return r;
-  if (nmat == 2) {
-    if (int r = get_map(a->qw2, a->N, rows, tr, &p.map[1])) return r;
-  }
-  p.sz[0] = a->sz; p.sz[1] = a->sz2;
-  p.nmat = nmat; p.N = a->N; p.K = a->K; p.group = a->group;
-  p.G = (a->K + a->group - 1) / a->group;
-  p.M = a->M;
+  p.w[0] = a->w; p.w[1] = a->w2;
+  p.nmat = nmat; p.N = a->N; p.K = a->K; p.group = a->group; p.M = a->M;
+  p.G = pl.G; p.GT = pl.GT; p.ntiles = pl.ntiles; p.I = pl.I;
   p.x = (const __nv_bfloat16*)a->x;
   p.norm_w = (const __nv_bfloat16*)a->norm_weight;
   p.ssq = a->ssq; p.ssq_parts = a->ssq_parts; p.eps = a->eps;
@@ -586,25 +661,16 @@ int ll_int4_gemv(const ll_gemv_args* a, ll_stream stream) {
   p.rope = a->rope; p.pos = a->pos;
   p.k_cache = (__nv_bfloat16*)a->k_cache; p.v_cache = (__nv_bfloat16*)a->v_cache;
   p.n_head = a->n_head; p.head_size = a->head_size; p.cache_len = a->cache_len;
-  p.partials = a->partials; p.counters = a->counters;
-  p.nchunks = (a->N + CHUNK - 1) / CHUNK;
-  p.ktiles = (rows + tr - 1) / tr;
-  const int sms = sm_count();
-  int ks = a->ksplit > 0 ? a->ksplit : choose_ksplit(a->N, a->K, a->group, nmat, a->M, tr, sms);
-  if (ks > p.ktiles) ks = p.ktiles;
-  p.tiles_per_split = (p.ktiles + ks - 1) / ks;
-  ks = (p.ktiles + p.tiles_per_split - 1) / p.tiles_per_split;
-  p.ksplit = ks;
-  LL_CHECK_ARG((long)p.tiles_per_split * 2 * tr * a->M * 2 <= 64 * 1024, "K slice too large for shared memory; raise ksplit");
-  LL_CHECK_ARG(ks <= MAX_KSPLIT, "ksplit must be <= %d", MAX_KSPLIT);
-  if (nmat * ks > 1) LL_CHECK_ARG(a->partials && a->counters, "split-K / two-matrix launch needs partials and counters scratch");
-  p.nunits = p.nchunks * nmat * ks;
-  p.xs_stride = p.tiles_per_split * 2 * tr + 8;
+  p.partials = a->partials; p.counters = a->counters; p.maxc = pl.maxc;
+  p.S = pl.S; p.xs_stride = pl.xs_stride; p.ts_max = pl.ts_max;
+  p.off_xs = pl.off_xs; p.off_sx = pl.off_sx; p.off_red = pl.off_red; p.off_cta = pl.off_cta;
+  p.off_wv = pl.off_wv; p.off_bar = pl.off_bar;
 
   cudaStream_t st = (cudaStream_t)stream;
-  if (tr == 64) return launch_cfg<Cfg<4, 2, 64>>(p, a, st);
-  if (tr == 32) return launch_cfg<Cfg<4, 2, 32>>(p, a, st);
-  return launch_cfg<Cfg<4, 2, 16>>(p, a, st);
+  const bool pdl = (a->flags & LL_GEMV_PDL) != 0;
+  if (pl.W == 12) return launch_w<12>(p, pl, pdl, st);
+  if (pl.W == 8) return launch_w<8>(p, pl, pdl, st);
+  return launch_w<4>(p, pl, pdl, st);
 }
 
 }  // extern "C"

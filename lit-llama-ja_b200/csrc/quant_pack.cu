@@ -1,4 +1,4 @@
-// GPTQ column-block storage kernels: pack, unpack, reference-semantics linear, int4 side table.
+// GPTQ column-block storage kernels: pack, unpack, reference-semantics linear.
 // ref: /root/reference/lit_llama/quantization.py:339-421 (ColBlockQuantizedLinear).
 #include <stdarg.h>
 
@@ -137,20 +137,6 @@ __global__ void qlinear_simt_kernel(const A* __restrict__ x, int M, const uint8_
   }
 }
 
-// ---------------------------------------------------------------- int4 side table
-template <typename P>
-__global__ void int4_prepare_kernel(const P* __restrict__ scales, const P* __restrict__ zeros,
-                                    uint32_t* __restrict__ sz, int N, int G, int32_t* status) {
-  const int n = blockIdx.x * blockDim.x + threadIdx.x;
-  const int g = blockIdx.y;
-  if (n >= N) return;
-  const float s = dt<P>::ld(scales, (size_t)n * G + g);
-  const float z = dt<P>::ld(zeros, (size_t)n * G + g);
-  const float zz = 128.f + z;
-  if (!(bf16r(zz) == zz) || !(bf16r(s) == s) || !(bf16r(z) == z)) atomicExch(status, 1);
-  sz[(size_t)g * N + n] = (uint32_t)f32_to_bf16_bits(s) | ((uint32_t)f32_to_bf16_bits(zz) << 16);
-}
-
 int check_quant_args(int N, int K, int bits, int tile_cols, int* tile, int* G) {
   LL_CHECK_ARG(bits == 1 || bits == 2 || bits == 4 || bits == 8, "bits must be 1, 2, 4 or 8 (got %d)", bits);
   LL_CHECK_ARG(N > 0 && K > 0, "N and K must be positive (N=%d K=%d)", N, K);
@@ -244,22 +230,6 @@ int ll_qlinear_simt(const void* x, int adt, int M, const uint8_t* qw, const void
   }
 #undef QL
   LL_LAUNCH_OK("qlinear_simt_kernel");
-  return LL_OK;
-}
-
-int ll_int4_prepare(const void* scales, const void* zeros, int pdt, uint32_t* sz, int N, int G, int32_t* status,
-                    ll_stream stream) {
-  LL_CHECK_ARG(scales && zeros && sz && status, "null pointer");
-  LL_CHECK_ARG(N > 0 && G > 0 && G <= 65535, "bad N/G (%d, %d)", N, G);
-  dim3 block(128), grid((N + 127) / 128, G);
-  cudaStream_t st = (cudaStream_t)stream;
-  if (pdt == LL_F32) int4_prepare_kernel<float><<<grid, block, 0, st>>>((const float*)scales, (const float*)zeros, sz, N, G, status);
-  else if (pdt == LL_BF16) int4_prepare_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16*)scales, (const __nv_bfloat16*)zeros, sz, N, G, status);
-  else {
-    set_error("int4_prepare: unsupported param dtype %d", pdt);
-    return LL_ERR_UNSUPPORTED;
-  }
-  LL_LAUNCH_OK("int4_prepare_kernel");
   return LL_OK;
 }
 

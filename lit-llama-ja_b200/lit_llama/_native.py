@@ -31,14 +31,14 @@ vp, i32, sz_t = C.c_void_p, C.c_int, C.c_size_t
 class GemvArgs(C.Structure):
     """struct ll_gemv_args (include/llb200.h)."""
     _fields_ = [
-        ("qw", vp), ("sz", vp), ("qw2", vp), ("sz2", vp),
+        ("w", vp), ("w2", vp),
         ("N", C.c_int32), ("K", C.c_int32), ("group", C.c_int32), ("M", C.c_int32),
         ("x", vp), ("norm_weight", vp), ("ssq", vp), ("ssq_parts", C.c_int32), ("eps", C.c_float),
         ("epilogue", C.c_int32), ("flags", C.c_int32),
         ("y", vp), ("bias", vp), ("ssq_out", vp),
         ("rope", vp), ("pos", vp), ("k_cache", vp), ("v_cache", vp),
         ("n_head", C.c_int32), ("head_size", C.c_int32), ("cache_len", C.c_int32),
-        ("partials", vp), ("counters", vp), ("ksplit", C.c_int32),
+        ("partials", vp), ("counters", vp), ("grid", C.c_int32),
     ]
 
 
@@ -57,8 +57,9 @@ EXPORTS = {
     "ll_pack_weight": ([vp, i32, vp, vp, i32, vp, i32, i32, i32, i32, vp], C.c_int),
     "ll_get_weight": ([vp, vp, vp, i32, vp, i32, i32, i32, i32, i32, vp], C.c_int),
     "ll_qlinear_simt": ([vp, i32, i32, vp, vp, vp, i32, vp, vp, i32, i32, i32, i32, vp], C.c_int),
-    "ll_int4_prepare": ([vp, vp, i32, vp, i32, i32, vp, vp], C.c_int),
-    "ll_int4_gemv_plan": ([i32, i32, i32, i32, i32, C.POINTER(C.c_int32), C.POINTER(sz_t), C.POINTER(sz_t)], C.c_int),
+    "ll_int4_stream_bytes": ([i32, i32, i32], sz_t),
+    "ll_int4_prepare": ([vp, vp, vp, i32, vp, i32, i32, i32, vp, vp], C.c_int),
+    "ll_int4_gemv_plan": ([i32, i32, i32, i32, i32, i32, C.POINTER(sz_t), C.POINTER(sz_t)], C.c_int),
     "ll_int4_gemv": ([C.POINTER(GemvArgs), vp], C.c_int),
     "ll_rmsnorm": ([vp, vp, vp, i32, i32, i32, C.c_float, vp], C.c_int),
     "ll_embed_ssq": ([vp, vp, vp, vp, i32, i32, vp], C.c_int),
@@ -73,7 +74,8 @@ EXPORTS = {
 }
 _fn = {name: _proto(name, a, r) for name, (a, r) in EXPORTS.items()}
 
-if _fn["ll_abi_version"]() != 1:
+ABI_VERSION = 2
+if _fn["ll_abi_version"]() != ABI_VERSION:
     raise ImportError("libllb200.so ABI version mismatch; rebuild with lit-llama-ja_b200/build.py")
 
 
@@ -119,10 +121,19 @@ def stream() -> C.c_void_p:
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
-def gemv_plan(N: int, K: int, group: int, nmat: int, M: int):
-    ks, pb, cb = C.c_int32(), sz_t(), sz_t()
-    check(_fn["ll_int4_gemv_plan"](N, K, group, nmat, M, C.byref(ks), C.byref(pb), C.byref(cb)), "ll_int4_gemv_plan")
-    return ks.value, pb.value, cb.value
+def gemv_plan(N: int, K: int, group: int, nmat: int, M: int, grid: int = 0):
+    """(partial_bytes, counter_bytes) of scratch the GEMV needs; raises if the shape is unsupported."""
+    pb, cb = sz_t(), sz_t()
+    check(_fn["ll_int4_gemv_plan"](N, K, group, nmat, M, grid, C.byref(pb), C.byref(cb)), "ll_int4_gemv_plan")
+    return pb.value, cb.value
+
+
+def gemv_supported(N: int, K: int, group: int, nmat: int, M: int) -> bool:
+    return _fn["ll_int4_gemv_plan"](N, K, group, nmat, M, 0, None, None) == 0
+
+
+def stream_bytes(N: int, K: int, group: int) -> int:
+    return _fn["ll_int4_stream_bytes"](N, K, group)
 
 
 def gemv(args: GemvArgs) -> None:

@@ -36,7 +36,7 @@ class DecodeEngine:
     @staticmethod
     def eligible(model, B: int) -> bool:
         cfg = model.config
-        if B > DecodeEngine.MAX_BATCH or cfg.n_embd % 128 != 0 or cfg.head_size not in (32, 64, 128):
+        if B > DecodeEngine.MAX_BATCH or cfg.n_embd % 16 != 0 or cfg.head_size not in (32, 64, 128):
             return False
         wte = model.transformer.wte.weight
         if wte.device.type != "cuda" or wte.dtype != torch.bfloat16:
@@ -54,14 +54,18 @@ class DecodeEngine:
         for blk in model.transformer.h:
             if blk.mlp.c_fc1.tile_cols != blk.mlp.c_fc2.tile_cols:
                 return False
-        return True
+        E, H, V = cfg.n_embd, cfg.n_hidden, cfg.padded_vocab_size
+        h0 = model.transformer.h[0]
+        shapes = [(3 * E, E, h0.attn.c_attn.tile_cols, 1), (E, E, h0.attn.c_proj.tile_cols, 1),
+                  (H, E, h0.mlp.c_fc1.tile_cols, 2), (E, H, h0.mlp.c_proj.tile_cols, 1), (V, E, model.lm_head.tile_cols, 1)]
+        return all(N.gemv_supported(n, k, g, nmat, B) for n, k, g, nmat in shapes)
 
     def __init__(self, model, B: int, max_seq_length: int):
         cfg = model.config
         self.model, self.B, self.S = model, B, max_seq_length
         dev = model.transformer.wte.weight.device
         E, H, V = cfg.n_embd, cfg.n_hidden, cfg.padded_vocab_size
-        self.nparts = E // 128
+        self.nparts = E // 16
         bf, f32, i32 = torch.bfloat16, torch.float32, torch.int32
         self.tok = torch.zeros(B, dtype=torch.int64, device=dev)
         self.pos = torch.zeros(3, dtype=i32, device=dev)
@@ -79,7 +83,6 @@ class DecodeEngine:
 
         # split plans + scratch (owned by the engine: nothing is allocated during capture)
         pb_max, cb_max = 0, 0
-        self.plans = {}
         for name, (n, k, g, nmat) in {
             "attn": (3 * E, E, model.transformer.h[0].attn.c_attn.tile_cols, 1),
             "proj": (E, E, model.transformer.h[0].attn.c_proj.tile_cols, 1),
@@ -87,8 +90,7 @@ class DecodeEngine:
             "down": (E, H, model.transformer.h[0].mlp.c_proj.tile_cols, 1),
             "head": (V, E, model.lm_head.tile_cols, 1),
         }.items():
-            ks, pb, cb = N.gemv_plan(n, k, g, nmat, B)
-            self.plans[name] = ks
+            pb, cb = N.gemv_plan(n, k, g, nmat, B)
             pb_max, cb_max = max(pb_max, pb), max(cb_max, cb)
         self.partials = torch.empty(pb_max // 4 + 16, dtype=f32, device=dev)
         self.counters = torch.zeros(cb_max // 4 + 16, dtype=i32, device=dev)
@@ -115,9 +117,9 @@ class DecodeEngine:
     # ------------------------------------------------------------------ argument blocks
     def _gemv_args(self, lin, x, y, epi, plan, norm=None, lin2=None):
         a = N.GemvArgs()
-        a.qw, a.sz = lin.quant_weight.data_ptr(), lin._sz.data_ptr()
+        a.w = lin._stream.data_ptr()
         if lin2 is not None:
-            a.qw2, a.sz2 = lin2.quant_weight.data_ptr(), lin2._sz.data_ptr()
+            a.w2 = lin2._stream.data_ptr()
         a.N, a.K, a.group, a.M = lin.out_features, lin.in_features, lin.tile_cols, self.B
         a.x, a.y = x.data_ptr(), y.data_ptr()
         if norm is not None:
@@ -125,7 +127,7 @@ class DecodeEngine:
         a.epilogue, a.flags = epi, (N.GEMV_PDL if self.use_pdl else 0)
         if epi == N.EPI_RESIDUAL:
             a.ssq_out = self.ssq.data_ptr()
-        a.partials, a.counters, a.ksplit = self.partials.data_ptr(), self.counters.data_ptr(), self.plans[plan]
+        a.partials, a.counters, a.grid = self.partials.data_ptr(), self.counters.data_ptr(), 0
         return a
 
     def _build_args(self):

@@ -43,9 +43,9 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         self.register_buffer("zeros", torch.empty((out_features, n_groups)))
         assert isinstance(bias, bool)
         self.register_buffer("bias", torch.empty((out_features,)) if bias else None)
-        self._sz = None        # [G][N] uint32 side table for the int4 GEMV (built lazily)
-        self._sz_key = None
-        self._sz_ok = False
+        self._stream = None    # fragment-ordered repack of quant_weight/scales/zeros for the int4 GEMV (lazy)
+        self._stream_key = None
+        self._stream_ok = False
 
     # -- state-dict: accept a checkpoint whose group count differs from the constructor's
     # (``quantization("gptq.int4")`` always builds per-row modules, ref utils.py:179-191; a
@@ -59,7 +59,7 @@ class ColBlockQuantizedLinear(torch.nn.Module):
                 self.scales = torch.empty((self.out_features, g), dtype=self.scales.dtype, device=self.scales.device)
                 self.zeros = torch.empty_like(self.scales)
         super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)
-        self._sz = None
+        self._stream = None
 
     def _apply(self, fn, *args, **kwargs):
         # keep the reference's (1, out) strides of quant_weight across .to()/.cuda()
@@ -67,7 +67,7 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         super()._apply(fn, *args, **kwargs)
         if stride_ok and self.quant_weight.stride() != (1, self.out_features):
             self.quant_weight = self.quant_weight.t().contiguous().t()
-        self._sz = None
+        self._stream = None
         return self
 
     def _packed_ptr_ok(self):
@@ -87,7 +87,7 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         N.call("ll_pack_weight", N.ptr(weight), N.dtype_code(weight.dtype), N.ptr(self.scales.contiguous()),
                N.ptr(self.zeros.contiguous()), N.dtype_code(self.scales.dtype), N.ptr(qw), self.out_features,
                self.in_features, self.bits, self.tile_cols, N.stream())
-        self._sz = None
+        self._stream = None
 
     def get_weight(self, dtype=torch.float):
         """ref: quantization.py:390-409 - bit-exact de-quantisation to ``[out, in]`` in ``dtype``."""
@@ -99,35 +99,42 @@ class ColBlockQuantizedLinear(torch.nn.Module):
                self.in_features, self.bits, self.tile_cols, N.stream())
         return out
 
-    # ------------------------------------------------------------------ int4 GEMV side table
+    # ------------------------------------------------------------------ int4 GEMV weight stream
     def _fast_eligible(self) -> bool:
-        return (self.bits == 4 and self.out_features % 16 == 0 and self.in_features % 8 == 0
-                and self.tile_cols % 32 == 0 and self.in_features % self.tile_cols == 0
-                and self.scales.dtype == self.zeros.dtype)
+        return (self.bits == 4 and self.scales.dtype == self.zeros.dtype
+                and N.stream_bytes(self.out_features, self.in_features, self.tile_cols) > 0)
 
     def prepare(self):
-        """Build (once) the transposed ``[G][N]`` (scale, 128+zero) table the GEMV streams.
-        Returns it, or ``None`` when the layer cannot take the tensor-core GEMV bit-faithfully."""
-        key = (self.scales.data_ptr(), self.zeros.data_ptr(), self.scales._version, self.zeros._version)
-        if self._sz_key == key and self._sz is not None:
-            return self._sz if self._sz_ok else None
-        self._sz_key = key
+        """Build (once) the fragment-ordered weight stream the int4 GEMV reads (a derived cache of
+        ``quant_weight``/``scales``/``zeros``; the checkpoint-layout buffers stay the state).
+        Returns it, or ``None`` when the layer cannot take the tensor-core GEMV (shape, or
+        scales / zeros not exactly representable in bf16)."""
+        key = (self.quant_weight.data_ptr(), self.scales.data_ptr(), self.zeros.data_ptr(),
+               self.quant_weight._version, self.scales._version, self.zeros._version)
+        if self._stream_key == key and self._stream is not None:
+            return self._stream if self._stream_ok else None
+        self._stream_key = key
         if not self._fast_eligible():
-            self._sz, self._sz_ok = torch.empty(0), False
+            self._stream, self._stream_ok = torch.empty(0), False
             return None
+        qw = self._packed_ptr_ok()
         dev = self.scales.device
-        G = self.scales.shape[1]
-        sz = torch.empty((G, self.out_features), dtype=torch.int32, device=dev)
+        nbytes = N.stream_bytes(self.out_features, self.in_features, self.tile_cols)
+        buf = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         status = torch.zeros(1, dtype=torch.int32, device=dev)
-        N.call("ll_int4_prepare", N.ptr(self.scales.contiguous()), N.ptr(self.zeros.contiguous()),
-               N.dtype_code(self.scales.dtype), N.ptr(sz), self.out_features, G, N.ptr(status), N.stream())
-        self._sz, self._sz_ok = sz, int(status.item()) == 0
-        return self._sz if self._sz_ok else None
+        N.call("ll_int4_prepare", N.ptr(qw), N.ptr(self.scales.contiguous()), N.ptr(self.zeros.contiguous()),
+               N.dtype_code(self.scales.dtype), N.ptr(buf), self.out_features, self.in_features, self.tile_cols,
+               N.ptr(status), N.stream())
+        self._stream, self._stream_ok = buf, int(status.item()) == 0
+        self._stream_key = (self.quant_weight.data_ptr(), self.scales.data_ptr(), self.zeros.data_ptr(),
+                            self.quant_weight._version, self.scales._version, self.zeros._version)
+        return self._stream if self._stream_ok else None
 
     # ------------------------------------------------------------------ row F
     def forward(self, inp):
-        """ref: quantization.py:411-421.  M <= 8 bf16 rows: TMA-streamed int4 GEMV; small M in other
-        dtypes / bit widths: reference-semantics SIMT kernel; large M: dequant-GEMM."""
+        """ref: quantization.py:411-421.  M <= 8 bf16 rows: TMA-streamed int4 GEMV (exact (q - zero) * scale,
+        fp32 accumulation); small M in other dtypes / bit widths: reference-semantics SIMT kernel;
+        large M: dequant-GEMM."""
         qw = self._packed_ptr_ok()
         N.require_cuda(inp, qw)
         K, Nout = self.in_features, self.out_features
@@ -140,11 +147,13 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         if M == 0:
             return inp.new_empty(out_shape)
         y = torch.empty((M, Nout), device=inp.device, dtype=inp.dtype)
-        if inp.dtype == torch.bfloat16 and M <= 8 and torch.cuda.is_current_stream_capturing() is False \
-                and self.prepare() is not None:
+        fast = inp.dtype == torch.bfloat16 and M <= 8 and N.gemv_supported(Nout, K, self.tile_cols, 1, M)
+        if fast and torch.cuda.is_current_stream_capturing():
+            fast = self._stream is not None and self._stream_ok   # the stream must have been prepared before capture
+        elif fast:
+            fast = self.prepare() is not None
+        if fast:
             self._gemv(x, y)
-        elif inp.dtype == torch.bfloat16 and M <= 8 and self._sz is not None and self._sz_ok:
-            self._gemv(x, y)  # under graph capture: table must have been prepared before
         elif M <= 16:
             assert inp.dtype in (torch.float32, torch.bfloat16)
             N.call("ll_qlinear_simt", N.ptr(x), N.dtype_code(x.dtype), M, N.ptr(qw), N.ptr(self.scales.contiguous()),
@@ -154,18 +163,18 @@ class ColBlockQuantizedLinear(torch.nn.Module):
             y = dequant_gemm(self, x)
         return y.reshape(out_shape)
 
-    def _gemv(self, x, y, *, pdl=False):
+    def _gemv(self, x, y, *, pdl=False, grid=0):
         ws = N.Workspace.get(x.device)
         M = x.shape[0]
-        ks, pb, cb = N.gemv_plan(self.out_features, self.in_features, self.tile_cols, 1, M)
+        pb, cb = N.gemv_plan(self.out_features, self.in_features, self.tile_cols, 1, M, grid)
         ws.ensure(pb, cb)
         a = N.GemvArgs()
-        a.qw, a.sz = self.quant_weight.data_ptr(), self._sz.data_ptr()
+        a.w = self._stream.data_ptr()
         a.N, a.K, a.group, a.M = self.out_features, self.in_features, self.tile_cols, M
         a.x, a.y = x.data_ptr(), y.data_ptr()
         a.bias = 0 if self.bias is None else self.bias.data_ptr()
         a.epilogue, a.flags = N.EPI_STORE, (N.GEMV_PDL if pdl else 0)
-        a.partials, a.counters, a.ksplit = ws.partials.data_ptr(), ws.counters.data_ptr(), ks
+        a.partials, a.counters, a.grid = ws.partials.data_ptr(), ws.counters.data_ptr(), grid
         N.gemv(a)
 
 
@@ -188,8 +197,8 @@ def qlinear_4bit_weight(inp, weight, scales, zeros):
     torch.nn.Module.__init__(lin)
     lin.in_features, lin.out_features, lin.bits, lin.entries_per_byte, lin.tile_cols = K, weight.shape[0], 4, 2, K
     lin.quant_weight, lin.scales, lin.zeros, lin.bias = weight, scales, zeros, None
-    lin._sz = lin._sz_key = None
-    lin._sz_ok = False
+    lin._stream = lin._stream_key = None
+    lin._stream_ok = False
     return lin(inp)
 
 

@@ -1,6 +1,6 @@
 """Standalone int4-GEMV microbenchmark / ncu target: the five 7B layer shapes at M=1, random packed
-weights (group 128).  Prints per-shape device time and achieved GB/s (CUDA events, L2 flushed by
-cycling through enough distinct weight copies)."""
+weights (group 128).  Prints per-shape device time and achieved GB/s (CUDA events, L2 defeated by
+cycling through >400 MB of distinct weight streams).  argv: reps [shape-name] [M] [grid]"""
 import sys
 from pathlib import Path
 
@@ -14,31 +14,38 @@ dev = torch.device("cuda:0")
 SHAPES = {"c_attn": (12288, 4096, 1), "attn.c_proj": (4096, 4096, 1), "fc1|fc2": (11008, 4096, 2),
           "mlp.c_proj": (4096, 11008, 1), "lm_head": (32000, 4096, 1)}
 GROUP = 128
+import numpy as np  # noqa: E402
+TAIL = torch.from_numpy(np.array([0xC1C03C24] * 16, dtype=np.uint32).view(np.uint8).copy()).to(dev)  # bf16 (0.01, -24.0)
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 20
-only = sys.argv[2] if len(sys.argv) > 2 else None
+only = sys.argv[2] if len(sys.argv) > 2 and sys.argv[2] != "all" else None
 M = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+grid = int(sys.argv[4]) if len(sys.argv) > 4 else 0
 
 for name, (n, k, nmat) in SHAPES.items():
     if only and only != name:
         continue
-    bytes_one = nmat * (n * k // 2 + 4 * n * (k // GROUP))
-    copies = max(2, int(400e6 // bytes_one) + 1)          # > 3x L2 worth of distinct weights
-    qws = [torch.randint(0, 256, (nmat, k // 2, n), dtype=torch.uint8, device=dev) for _ in range(copies)]
-    s = (torch.rand((nmat, k // GROUP, n), device=dev) * 0.01 + 0.001).bfloat16().view(torch.int16).int() & 0xffff
-    z = (torch.randint(0, 16, (nmat, k // GROUP, n), device=dev) + 128).bfloat16().view(torch.int16).int() & 0xffff
-    sz = (s | (z << 16)).int().contiguous()
+    sb = NV.stream_bytes(n, k, GROUP)
+    alg = nmat * (n * k // 2 + 4 * n * (k // GROUP)) + 2 * (n + k)
+    copies = max(2, int(400e6 // (nmat * sb)) + 1)
+    # random stream bytes: nibbles random; tails = (scale 0.01, -(16+8)) so results stay finite
+    ws_ = []
+    for _ in range(copies):
+        w = torch.randint(0, 256, (nmat, sb), dtype=torch.uint8, device=dev)
+        blk = w.view(nmat, -1, 1088)
+        blk[:, :, 1024:] = TAIL
+        ws_.append(w)
     x = torch.randn((M, k), device=dev).bfloat16()
     y = torch.empty((M, n), device=dev, dtype=torch.bfloat16)
-    ks, pb, cb = NV.gemv_plan(n, k, GROUP, nmat, M)
+    pb, cb = NV.gemv_plan(n, k, GROUP, nmat, M, grid)
     ws = NV.Workspace.get(dev).ensure(pb, cb)
     args = []
-    for qw in qws:
+    for w in ws_:
         a = NV.GemvArgs()
-        a.qw, a.sz = qw[0].data_ptr(), sz[0].data_ptr()
+        a.w = w[0].data_ptr()
         if nmat == 2:
-            a.qw2, a.sz2, a.epilogue = qw[1].data_ptr(), sz[1].data_ptr(), NV.EPI_SWIGLU
+            a.w2, a.epilogue = w[1].data_ptr(), NV.EPI_SWIGLU
         a.N, a.K, a.group, a.M, a.x, a.y = n, k, GROUP, M, x.data_ptr(), y.data_ptr()
-        a.partials, a.counters, a.ksplit = ws.partials.data_ptr(), ws.counters.data_ptr(), ks
+        a.partials, a.counters, a.grid = ws.partials.data_ptr(), ws.counters.data_ptr(), grid
         args.append(a)
     for a in args[:2]:
         NV.gemv(a)
@@ -50,4 +57,5 @@ for name, (n, k, nmat) in SHAPES.items():
     e1.record()
     torch.cuda.synchronize()
     us = 1e3 * e0.elapsed_time(e1) / reps
-    print(f"{name:12s} N={n:6d} K={k:6d} nmat={nmat} M={M} ksplit={ks:2d}  {us:8.2f} us  {bytes_one / us / 1e3:8.1f} GB/s", flush=True)
+    print(f"{name:12s} N={n:6d} K={k:6d} nmat={nmat} M={M} grid={grid or 'sm'}  {us:8.2f} us  "
+          f"{alg / us / 1e3:8.1f} GB/s algorithmic ({nmat * sb / us / 1e3:8.1f} GB/s streamed)", flush=True)

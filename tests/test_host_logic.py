@@ -18,7 +18,7 @@ def test_library_exports_every_declared_symbol():
     assert declared == set(_native.EXPORTS), declared ^ set(_native.EXPORTS)
     for name in declared:
         assert getattr(_native.lib, name) is not None
-    assert _native._fn["ll_abi_version"]() == 1
+    assert _native._fn["ll_abi_version"]() == _native.ABI_VERSION
 
 
 def test_quantization_ctx_swaps_and_restores():
