@@ -155,6 +155,15 @@ __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint3
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
+// Every kernel of the decode chain asks for the maximum shared-memory carve-out: an SM cannot change its
+// L1/shared split while a CTA is resident, so under programmatic dependent launch a kernel that prefers
+// a different split than its (co-resident) predecessor waits for the SM to drain - measured: +12 us per
+// c_proj -> fc edge, +25 us per block, when the chain started on a small-smem kernel.
+template <typename F>
+inline void prefer_max_smem(F* kernel) {
+  cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+}
+
 // Launch helper: optional programmatic-stream-serialization attribute (PDL).
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, bool pdl,

@@ -297,6 +297,8 @@ int ll_rmsnorm(const void* x, const void* w, void* y, int dtype, int rows, int d
 int ll_embed_ssq(const void* wte, const int64_t* idx, void* x, float* ssq, int M, int dim, ll_stream stream) {
   LL_CHECK_ARG(wte && idx && x && ssq && M > 0 && dim > 0 && dim % 16 == 0, "bad embed arguments (dim must be a multiple of 16)");
   const int nchunks = (dim + 127) / 128;
+  static bool once = false;
+  if (!once) { prefer_max_smem(embed_ssq_kernel); prefer_max_smem(set_pos_kernel); prefer_max_smem(advance_pos_kernel); once = true; }
   embed_ssq_kernel<<<dim3(nchunks, M), 128, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)wte, idx, (__nv_bfloat16*)x, ssq, dim, dim / 16);
   LL_LAUNCH_OK("embed_ssq_kernel");
   return LL_OK;
@@ -334,8 +336,15 @@ int ll_decode_attn(const void* q, const void* k_cache, const void* v_cache, cons
   cudaStream_t st = (cudaStream_t)stream;
   const bool pdl = (flags & LL_GEMV_PDL) != 0;
 #define ATTN(TT, HS)                                                                                              \
-  LL_CUDA(launch(decode_attn_kernel<TT, HS>, grid, block, 0, st, pdl, (const TT*)q, (const TT*)k_cache,          \
-                 (const TT*)v_cache, pos, (TT*)y, n_head, cache_len, max_splits, scratch, counters, pdl ? 1 : 0))
+  do {                                                                                                            \
+    static bool once = false;                                                                                     \
+    if (!once) {                                                                                                  \
+      prefer_max_smem(decode_attn_kernel<TT, HS>);                                                                \
+      once = true;                                                                                                \
+    }                                                                                                             \
+    LL_CUDA(launch(decode_attn_kernel<TT, HS>, grid, block, 0, st, pdl, (const TT*)q, (const TT*)k_cache,        \
+                   (const TT*)v_cache, pos, (TT*)y, n_head, cache_len, max_splits, scratch, counters, pdl ? 1 : 0)); \
+  } while (0)
   if (dtype == LL_BF16) {
     if (head_size == 128) ATTN(__nv_bfloat16, 128);
     else if (head_size == 64) ATTN(__nv_bfloat16, 64);

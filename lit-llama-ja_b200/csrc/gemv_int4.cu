@@ -564,6 +564,7 @@ template <int W, int KSP>
 int launch_cfg(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
   static size_t configured = 0;
   if (pl.smem > configured) {
+    if (configured == 0) prefer_max_smem(gemv_int4_kernel<W, KSP>);
     LL_CUDA(cudaFuncSetAttribute(gemv_int4_kernel<W, KSP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
     configured = pl.smem;
   }

@@ -78,6 +78,9 @@ class DecodeEngine:
         self.rope = model._rope_f32
         self.use_pdl = _env_flag("LLB200_PDL", True)
         self.use_graph = _env_flag("LLB200_GRAPH", True)
+        # measured (profiles/r01_step_probe.md): launching the attention kernel itself with the programmatic
+        # attribute costs ~8 us per block (its 512 waiting CTAs crowd the SMs the GEMV pair shares)
+        self.attn_pdl = _env_flag("LLB200_PDL_ATTN", False)
         self.n_launches = 0
         self.n_replays = 0
 
@@ -153,7 +156,7 @@ class DecodeEngine:
         st = N.stream()
         wte = self.model.transformer.wte.weight
         N.call("ll_embed_ssq", N.ptr(wte), N.ptr(self.tok), N.ptr(self.x), N.ptr(self.ssq), self.B, cfg.n_embd, st)
-        flags = N.GEMV_PDL if self.use_pdl else 0
+        flags = N.GEMV_PDL if (self.use_pdl and self.attn_pdl) else 0
         n = 1
         for a_attn, kc, vc, a_proj, a_fc, a_down in self.layers:
             N.gemv(a_attn)
