@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define LL_ABI_VERSION 2
+#define LL_ABI_VERSION 3
 
 #define LL_OK 0
 #define LL_ERR_ARG (-1)         /* bad shape / dtype / null pointer */
@@ -99,7 +99,7 @@ LL_API int ll_int4_prepare(const uint8_t* qw, const void* scales, const void* ze
                     int N, int K, int group, int32_t* status, ll_stream stream);
 
 #define LL_EPI_STORE 0    /* y = bf16(acc (+bias)) */
-#define LL_EPI_RESIDUAL 1 /* y (residual stream, in place) = bf16(y + bf16(acc)); ssq_out partials */
+#define LL_EPI_RESIDUAL 1 /* y (residual stream, in place) = bf16(y + bf16(acc)) */
 #define LL_EPI_ROPE_KV 2  /* c_attn: RoPE on q,k; q -> y, k,v -> KV cache at pos[1] */
 #define LL_EPI_SWIGLU 3   /* y = bf16(bf16(silu(bf16(accA))) * bf16(accB)), accB from w2 */
 
@@ -112,32 +112,25 @@ typedef struct ll_gemv_args {
   int32_t M;           /* rows of x, 1..8 */
   const void* x;       /* [M][K] bf16 */
   /* optional fused RMSNorm on x (ref: model.py:276-283): x_used = bf16(w * bf16(x * r)),
-   * r from the ssq partials: mean = bf16(sum(ssq[m][:]) / K) */
+   * r = bf16(rsqrt(bf16(bf16(sum(bf16(x*x)) / K) + eps))), computed by every CTA from its staged row */
   const void* norm_weight; /* [K] bf16 or NULL */
-  const float* ssq;        /* [M][ssq_parts] partial sums of bf16(x*x) */
-  int32_t ssq_parts;
   float eps;
   int32_t epilogue;
   int32_t flags;
   void* y;          /* see LL_EPI_* ; [M][N] bf16 (ROPE_KV: q [M][N/3]) */
   const void* bias; /* [N] bf16 or NULL (LL_EPI_STORE) */
-  float* ssq_out;   /* LL_EPI_RESIDUAL: [M][N/16] (one partial per 16-column tile) */
   /* LL_EPI_ROPE_KV (ref: model.py:204-228, 312-329) */
   const float* rope;  /* [block_size][head_size/2][2] fp32 (cos, sin) */
   const int32_t* pos; /* device int32[3]: rope position, cache slot, #valid slots */
   void* k_cache;      /* [M][n_head][cache_len][head_size] bf16 */
   void* v_cache;
   int32_t n_head, head_size, cache_len;
-  /* cross-CTA scratch for tiles whose k range is shared by several CTAs (see ll_int4_gemv_plan) */
-  float* partials;
-  int32_t* counters; /* zero before first use; the kernel leaves them zero */
-  int32_t grid;      /* 0 = one CTA per SM; >0 forces the CTA count (tests) */
+  int32_t grid; /* 0 = one CTA per SM; >0 forces the CTA count (tests).  CTAs own whole 16-column tiles. */
 } ll_gemv_args;
 
-/* Host query: scratch sizes for (N, K, group, nmat, M) at the CTA count the library would use
- * (or `grid` if > 0).  Returns LL_ERR_UNSUPPORTED when the shape does not fit the kernel. */
-LL_API int ll_int4_gemv_plan(int N, int K, int group, int nmat, int M, int grid, size_t* partial_bytes,
-                      size_t* counter_bytes);
+/* Host query: LL_OK if the GEMV takes (N, K, group, nmat, M) (LL_ERR_UNSUPPORTED otherwise, e.g. M*K too
+ * large for shared memory); *smem_bytes / *ctas (optional) report the launch it would use. */
+LL_API int ll_int4_gemv_plan(int N, int K, int group, int nmat, int M, int grid, size_t* smem_bytes, int32_t* ctas);
 LL_API int ll_int4_gemv(const ll_gemv_args* args /* host */, ll_stream stream);
 
 /* ---------------------------------------------------------------------------------------
@@ -148,7 +141,8 @@ LL_API int ll_int4_gemv(const ll_gemv_args* args /* host */, ll_stream stream);
 LL_API int ll_rmsnorm(const void* x, const void* weight, void* y, int dtype, int rows, int dim, float eps, ll_stream stream);
 
 /* ref: wte lookup, model.py:110, fused with the sum-of-squares partials the first fused RMSNorm
- * consumes: x[m][:] = wte[idx[m]][:]; ssq[m][p] = sum over 16-column tile p of bf16(x*x). */
+ * consumes: x[m][:] = wte[idx[m]][:]; ssq (optional, may be NULL): ssq[m][p] = sum over 16-column tile p of
+ * bf16(x*x). */
 LL_API int ll_embed_ssq(const void* wte, const int64_t* idx, void* x, float* ssq, int M, int dim, ll_stream stream);
 
 /* ref: apply_rope (model.py:312-329) on q and k of a fused qkv row + KV-cache write (model.py:218-228,

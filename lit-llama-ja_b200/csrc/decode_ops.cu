@@ -54,7 +54,7 @@ __global__ void embed_ssq_kernel(const __nv_bfloat16* __restrict__ wte, const in
   v += __shfl_xor_sync(0xffffffffu, v, 2);
   v += __shfl_xor_sync(0xffffffffu, v, 1);
   const int part = n >> 4;
-  if ((threadIdx.x & 15) == 0 && part < nparts) ssq[m * nparts + part] = v;
+  if (ssq != nullptr && (threadIdx.x & 15) == 0 && part < nparts) ssq[m * nparts + part] = v;
 }
 
 // ---------------------------------------------------------------- RoPE + KV append (rows R, A)
@@ -295,7 +295,7 @@ int ll_rmsnorm(const void* x, const void* w, void* y, int dtype, int rows, int d
 }
 
 int ll_embed_ssq(const void* wte, const int64_t* idx, void* x, float* ssq, int M, int dim, ll_stream stream) {
-  LL_CHECK_ARG(wte && idx && x && ssq && M > 0 && dim > 0 && dim % 16 == 0, "bad embed arguments (dim must be a multiple of 16)");
+  LL_CHECK_ARG(wte && idx && x && M > 0 && dim > 0 && dim % 16 == 0, "bad embed arguments (dim must be a multiple of 16)");
   const int nchunks = (dim + 127) / 128;
   static bool once = false;
   if (!once) { prefer_max_smem(embed_ssq_kernel); prefer_max_smem(set_pos_kernel); prefer_max_smem(advance_pos_kernel); once = true; }

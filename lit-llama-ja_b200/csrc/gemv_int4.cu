@@ -20,13 +20,16 @@
 //    LOP3/SHF, mma.sync m16n8k16 (bf16 x bf16 -> fp32) with the weights as the A operand and up to
 //    8 batch rows of x as the B columns.  Per block: acc starts at -(16+zero)*sum(x_block), ends as
 //    sum (q-zero) x, and is folded into the running column sums with one FFMA by the scale.
-//  * x is staged once per CTA in shared memory in natural order (optionally through the fused
-//    RMSNorm, ref model.py:276-283 rounding steps) together with its per-block sums.
+//  * x is staged once per CTA in shared memory by one bulk copy per row; the optional fused RMSNorm
+//    (ref model.py:276-283 rounding steps) is computed in place from the staged row (its sum of squares
+//    included: every CTA holds the whole row), together with the per-block sums of x.
 //  * Fixed-order reduction across warps in shared memory; tiles whose k range is shared by several
 //    CTAs go through a global scratch and the LAST-arriving contributor sums them in contributor
 //    order (deterministic, self-resetting counters) and runs the fused epilogue: plain store,
 //    residual add (+ RMSNorm sum-of-squares partials for the next kernel), RoPE + KV-cache write
 //    (c_attn), or SwiGLU (c_fc1/c_fc2 as two matrices of one launch).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace llb {
@@ -54,27 +57,33 @@ struct Params {
   int I;       // total items
   const __nv_bfloat16* x;
   const __nv_bfloat16* norm_w;
-  const float* ssq;
-  int ssq_parts;
   float eps;
   int epilogue;
   __nv_bfloat16* y;
   const __nv_bfloat16* bias;
-  float* ssq_out;
   const float* rope;
   const int32_t* pos;
   __nv_bfloat16* k_cache;
   __nv_bfloat16* v_cache;
   int n_head, head_size, cache_len;
-  float* partials;
-  int32_t* counters;
-  int maxc;  // contributor slots per tile in `partials`
   // shared-memory plan
   int S;          // ring slots
   int xs_stride;  // bytes per staged x row
   int ts_max;     // (tile, matrix) slots of the cross-warp reduction
-  int off_xs, off_sx, off_red, off_cta, off_wv, off_bar;
+  int off_xs, off_sx, off_red, off_wv, off_bar, off_nw;
+  int prefetch_delay_ns;  // producer start delay under PDL (lets the running kernel's x staging go first)
+  unsigned long long* trace;  // debug: [P][8] globaltimer stamps of this launch, or nullptr
 };
+
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define TRACE(i)                                                                   \
+  do {                                                                             \
+    if (p.trace != nullptr && threadIdx.x == 0) p.trace[blockIdx.x * 16 + (i)] = gtimer(); \
+  } while (0)
 
 __device__ __forceinline__ void consumer_sync(int n) { asm volatile("bar.sync 1, %0;" ::"r"(n) : "memory"); }
 
@@ -107,32 +116,56 @@ __device__ __forceinline__ int range_owner(int x, int I, int P) {
 constexpr uint32_t NIB_MASK = 0x00780078u;   // nibble at bits 3..6 of each bf16 half
 constexpr uint32_t NIB_MAGIC = 0x41804180u;  // bf16 16.0: 16 + q exact for q in 0..15
 
-template <int W, int KSP>
-__global__ void __launch_bounds__((W + 1) * 32, (W >= 12) ? 2 : 1) gemv_int4_kernel(const __grid_constant__ Params p) {
+// spin on an mbarrier phase (try_wait suspends in hardware up to a time limit, so this is not a hot loop)
+__device__ __forceinline__ void mbar_wait_u32(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n"
+      "LLB_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra LLB_DONE;\n\t"
+      "bra LLB_WAIT;\n"
+      "LLB_DONE:\n\t}" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void st_release_gpu(int32_t* p, int32_t v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int32_t ld_acquire_gpu(const int32_t* p) {
+  int32_t v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+template <int W, int KSP, int BPW>
+__global__ void __launch_bounds__((W + 1) * 32, 2) gemv_int4_kernel(const __grid_constant__ Params p) {
   constexpr int KB = 32 * KSP;
   constexpr int BLK = KB * 8 + TAIL_BYTES;
-  constexpr int CH = W;  // items per chunk: one per consumer warp
+  constexpr int CH = W * BPW;  // items per chunk: BPW consecutive blocks per consumer warp
   constexpr int CHB = CH * BLK;
   constexpr int NCONS = W * 32;
   constexpr int LPB = KB / 8;  // lanes staging one k-block of x (8 elements each)
+  constexpr int MAX_SLOTS_C = 12;
 
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* ring = smem;
-  uint8_t* xs = smem + p.off_xs;
+  uint8_t* xs = smem + p.off_xs;                            // [M+1][xs_stride] bf16, last row zero
   float* sx = reinterpret_cast<float*>(smem + p.off_sx);    // [G][8]
   float* red = reinterpret_cast<float*>(smem + p.off_red);  // [ts_max][W][M][16]
-  float* cta = reinterpret_cast<float*>(smem + p.off_cta);  // [ts_max][M][16]
   float* wv = reinterpret_cast<float*>(smem + p.off_wv);    // [W][nmat][M][16]
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + p.off_bar);
   uint64_t* empty = full + p.S;
-  __shared__ float s_rnorm[MAXM];
+  __shared__ float s_rnorm[W][MAXM];
+  __shared__ float s_part[W][MAXM];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int P = gridDim.x, c = blockIdx.x;
-  const int i0 = range_start(c, p.I, P), i1 = range_start(c + 1, p.I, P);
+  // whole tiles per CTA: no tile is shared between CTAs, so no cross-CTA exchange on the critical path
+  const int i0 = range_start(c, p.ntiles, P) * p.GT, i1 = range_start(c + 1, p.ntiles, P) * p.GT;
   const int nch = (i1 - i0 + CH - 1) / CH;
   const int G = p.G, S = p.S, M = p.M;
 
+  TRACE(0);
   if (threadIdx.x == 0) {
     for (int i = 0; i < S; ++i) {
       mbar_init(&full[i], 1);
@@ -147,26 +180,32 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12) ? 2 : 1) gemv_int4_ker
     // =============================== producer warp ===============================
     if (lane == 0) {
       const uint64_t pol = policy_evict_first();
+      if (p.prefetch_delay_ns > 0) __nanosleep(p.prefetch_delay_ns);
       int slot = 0;
       uint32_t phase = 1;  // parity of the PREVIOUS use of the slot once the ring wraps
+      int it = i0;
+      int vt = it / G, g = it - vt * G;
       for (int ch = 0; ch < nch; ++ch, ++slot) {
         if (slot == S) {
           slot = 0;
           phase ^= 1u;
         }
-        if (ch >= S) mbar_wait(&empty[slot], phase);
-        const int a = i0 + ch * CH, b = min(a + CH, i1);
-        mbar_expect_tx(&full[slot], (uint32_t)(b - a) * BLK);
+        if (ch >= S) mbar_wait_u32(smem_u32(&empty[slot]), phase);
+        const int b = min(it + CH, i1);
+        mbar_expect_tx(&full[slot], (uint32_t)(b - it) * BLK);
         uint8_t* dst = ring + (size_t)slot * CHB;
-        int it = a;
         while (it < b) {  // contiguous runs: a run ends where the (tile, matrix) changes
-          const int vt = it / G, g = it - vt * G;
           const int run = min(G - g, b - it);
           const int mat = p.nmat == 2 ? (vt & 1) : 0, tile = p.nmat == 2 ? (vt >> 1) : vt;
           const uint8_t* src = p.w[mat] + ((size_t)tile * G + g) * BLK;
           bulk_load_1d_hint(dst, src, (uint32_t)run * BLK, &full[slot], pol);
           dst += (size_t)run * BLK;
           it += run;
+          g += run;
+          if (g == G) {
+            g = 0;
+            ++vt;
+          }
         }
       }
     }
@@ -179,68 +218,147 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12) ? 2 : 1) gemv_int4_ker
   const int vt_first = i0 / G, vt_last = (i1 - 1) / G;
   const int nvt = vt_last - vt_first + 1;
   const int MT = M * TILE_N;  // floats per (tile, matrix) result
+  const bool has_norm = p.norm_w != nullptr;
+  const int vpr = p.K >> 3;
 
-  for (int i = ctid; i < p.ts_max * W * MT; i += NCONS) red[i] = 0.f;
+  // norm weights are constants: their bulk copy into shared memory starts before the previous kernel ends
+  uint8_t* nws = smem + p.off_nw;  // [K] bf16 (only with the fused RMSNorm)
+  uint64_t* xbar = full + 2 * MAX_SLOTS_C;  // [0]: x rows landed, [1]: norm weights landed
+  if (ctid == 0) {
+    mbar_init(&xbar[0], 1);
+    mbar_init(&xbar[1], 1);
+    fence_barrier_init();
+    if (has_norm) {
+      mbar_expect_tx(&xbar[1], (uint32_t)p.K * 2);
+      bulk_load_1d(nws, p.norm_w, (uint32_t)p.K * 2, &xbar[1]);
+    }
+  }
+  for (int i = ctid; i < nvt * W * MT; i += NCONS) red[i] = 0.f;
   for (int i = ctid; i < G * 8; i += NCONS) sx[i] = 0.f;
+  for (int i = ctid; i < (p.K >> 2); i += NCONS) *reinterpret_cast<uint2*>(xs + (size_t)M * p.xs_stride + i * 8) = make_uint2(0u, 0u);
   consumer_sync(NCONS);
 
+  TRACE(1);
   pdl_wait();  // activations (x, ssq, residual, caches, scratch) come from earlier kernels
+  TRACE(2);
+  int rope_pos = 0, kv_slot = 0;
+  if (p.epilogue == LL_EPI_ROPE_KV) {
+    rope_pos = p.pos[0];
+    kv_slot = p.pos[1];
+  }
 
-  // ---- stage x (natural order, optional fused RMSNorm) and its per-k-block sums
-  if (p.norm_w != nullptr) {
-    for (int m = warp; m < M; m += W) {
-      float s = 0.f;
-      for (int i = lane; i < p.ssq_parts; i += 32) s += p.ssq[m * p.ssq_parts + i];
-      s = warp_sum(s);
-      if (lane == 0) {
-        const float mean = bf16r(s * (1.0f / (float)p.K));
-        s_rnorm[m] = bf16r(rsqrtf(bf16r(mean + p.eps)));
+  // ---- stage x: one bulk copy per row straight into shared memory (a single memory round trip whatever
+  //      K is), then normalise in place (optional fused RMSNorm) and form the per-k-block sums
+  if (ctid == 0) {
+    mbar_expect_tx(&xbar[0], (uint32_t)M * p.K * 2);
+    for (int m = 0; m < M; ++m) bulk_load_1d(xs + (size_t)m * p.xs_stride, p.x + (size_t)m * p.K, (uint32_t)p.K * 2, &xbar[0]);
+  }
+  if (has_norm) mbar_wait_u32(smem_u32(&xbar[1]), 0);
+  TRACE(8);
+  mbar_wait_u32(smem_u32(&xbar[0]), 0);
+  TRACE(9);
+  if (has_norm) {
+    // sum of squares of each row straight from the staged copy (every CTA holds the whole row): no
+    // partial sums handed over from the previous kernel, fixed summation order
+    for (int m = 0; m < M; ++m) {
+      float ss = 0.f;
+      for (int v = ctid; v < vpr; v += NCONS) {
+        const uint4 raw = *reinterpret_cast<const uint4*>(xs + (size_t)m * p.xs_stride + v * 16);
+        const uint32_t wd[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float x0 = bf16_bits_to_f32(wd[e] & 0xffffu), x1 = bf16_bits_to_f32(wd[e] >> 16);
+          ss += bf16r(__fmul_rn(x0, x0)) + bf16r(__fmul_rn(x1, x1));
+        }
       }
+      ss = warp_sum(ss);
+      if (lane == 0) s_part[warp][m] = ss;
     }
     consumer_sync(NCONS);
+    if (lane < M) {
+      float tot = 0.f;
+#pragma unroll
+      for (int w = 0; w < W; ++w) tot += s_part[w][lane];
+      const float mean = bf16r(tot * (1.0f / (float)p.K));
+      s_rnorm[warp][lane] = bf16r(rsqrtf(bf16r(mean + p.eps)));
+    }
+    __syncwarp();
+    TRACE(7);
   }
-  {
-    const int vpr = p.K >> 3, total = M * vpr;
-    for (int v0 = 0; v0 < total; v0 += NCONS) {
+  for (int m = 0; m < M; ++m) {
+    const float rn = has_norm ? s_rnorm[warp][m] : 0.f;
+    uint8_t* row = xs + (size_t)m * p.xs_stride;
+#pragma unroll 2
+    for (int v0 = 0; v0 < vpr; v0 += NCONS) {
       const int v = v0 + ctid;
-      const bool ok = v < total;
+      const bool ok = v < vpr;
       float part = 0.f;
-      int m = 0, k = 0;
       if (ok) {
-        m = v / vpr;
-        k = (v - m * vpr) << 3;
-        uint4 raw = *reinterpret_cast<const uint4*>(p.x + (size_t)m * p.K + k);
+        const uint4 raw = *reinterpret_cast<const uint4*>(row + v * 16);
         uint32_t wd[4] = {raw.x, raw.y, raw.z, raw.w};
-        if (p.norm_w != nullptr) {
-          const float rn = s_rnorm[m];
-          const uint4 nraw = *reinterpret_cast<const uint4*>(p.norm_w + k);
+        if (has_norm) {
+          const uint4 nraw = *reinterpret_cast<const uint4*>(nws + v * 16);
           const uint32_t nw[4] = {nraw.x, nraw.y, nraw.z, nraw.w};
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float x0 = bf16r(__fmul_rn(bf16_bits_to_f32(wd[j] & 0xffffu), rn));
-            const float x1 = bf16r(__fmul_rn(bf16_bits_to_f32(wd[j] >> 16), rn));
-            const uint32_t o0 = f32_to_bf16_bits(__fmul_rn(bf16_bits_to_f32(nw[j] & 0xffffu), x0));
-            const uint32_t o1 = f32_to_bf16_bits(__fmul_rn(bf16_bits_to_f32(nw[j] >> 16), x1));
-            wd[j] = o0 | (o1 << 16);
+          for (int e = 0; e < 4; ++e) {
+            const float x0 = bf16r(__fmul_rn(bf16_bits_to_f32(wd[e] & 0xffffu), rn));
+            const float x1 = bf16r(__fmul_rn(bf16_bits_to_f32(wd[e] >> 16), rn));
+            const uint32_t o0 = f32_to_bf16_bits(__fmul_rn(bf16_bits_to_f32(nw[e] & 0xffffu), x0));
+            const uint32_t o1 = f32_to_bf16_bits(__fmul_rn(bf16_bits_to_f32(nw[e] >> 16), x1));
+            wd[e] = o0 | (o1 << 16);
           }
+          *reinterpret_cast<uint4*>(row + v * 16) = make_uint4(wd[0], wd[1], wd[2], wd[3]);
         }
 #pragma unroll
-        for (int j = 0; j < 4; ++j) part += bf16_bits_to_f32(wd[j] & 0xffffu) + bf16_bits_to_f32(wd[j] >> 16);
-        *reinterpret_cast<uint4*>(xs + (size_t)m * p.xs_stride + k * 2) = make_uint4(wd[0], wd[1], wd[2], wd[3]);
+        for (int e = 0; e < 4; ++e) part += bf16_bits_to_f32(wd[e] & 0xffffu) + bf16_bits_to_f32(wd[e] >> 16);
       }
 #pragma unroll
       for (int o = LPB / 2; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-      if (ok && (lane % LPB) == 0) sx[(k / KB) * 8 + m] = part;
+      if (ok && (lane % LPB) == 0) sx[(v / LPB) * 8 + m] = part;
     }
   }
+  TRACE(10);
   consumer_sync(NCONS);
+  TRACE(3);
 
-  // ---- stream this CTA's items
+  // epilogue operands that do not depend on this kernel's sums (residual stream, bias, RoPE row) are
+  // fetched now for this warp's first tile, behind the main loop
+  const int nmat = p.nmat;
+  const int T_first = vt_first / nmat, T_last = vt_last / nmat;
+  auto load_pre = [&](int T, float (&pre)[4], float2 (&cs)[2]) {
+    const int n0 = T * TILE_N;
+    if (p.epilogue == LL_EPI_RESIDUAL) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int e = lane + 32 * j;
+        if (e < MT) pre[j] = __bfloat162float(p.y[(size_t)(e >> 4) * p.N + n0 + (e & 15)]);
+      }
+    } else if (p.epilogue == LL_EPI_STORE && p.bias != nullptr) {
+      pre[0] = __bfloat162float(p.bias[n0 + (lane & 15)]);
+    } else if (p.epilogue == LL_EPI_ROPE_KV) {
+      const int E = p.N / 3, hs = p.head_size;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int e = lane + 32 * j;
+        const int n = n0 + 2 * (e & 7);
+        const int part = n / E, d = (n - part * E) % hs;
+        if (e < M * (TILE_N / 2) && part < 2)
+          cs[j] = *reinterpret_cast<const float2*>(p.rope + ((size_t)rope_pos * (hs / 2) + d / 2) * 2);
+      }
+    }
+  };
+  float pre0[4] = {0.f, 0.f, 0.f, 0.f};
+  float2 cs0[2] = {make_float2(1.f, 0.f), make_float2(1.f, 0.f)};
+  if (T_first + warp <= T_last) load_pre(T_first + warp, pre0, cs0);
+
+  // ---- stream this CTA's items: BPW consecutive blocks per warp per chunk, computed as independent
+  //      MMA chains (ILP), then folded into the running column sums in item order
   float out[4] = {0.f, 0.f, 0.f, 0.f};
   int cur_vt = -1;
-  const uint32_t xs_lane = smem_u32(xs) + (uint32_t)(g * p.xs_stride + tig * 16);
+  const uint32_t xs_lane = smem_u32(xs) + (uint32_t)(min(g, M) * p.xs_stride + tig * 16);  // rows >= M read zeros
   const uint32_t sx_lane = smem_u32(sx) + (uint32_t)(tig * 8);
-  const bool has_x = g < M;
+  const uint32_t ring_u = smem_u32(ring) + (uint32_t)(warp * BPW * BLK);
+  const uint32_t full_u = smem_u32(full), empty_u = smem_u32(empty);
 
   auto flush = [&](int vt) {
     float* r = red + ((size_t)(vt - vt_first) * W + warp) * MT;
@@ -254,67 +372,83 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12) ? 2 : 1) gemv_int4_ker
       r[m1 * TILE_N + g + 8] = out[3];
     }
   };
+  auto mma_word = [&](float (&a)[4], uint32_t w, uint32_t b0, uint32_t b1) {
+    const uint32_t a0 = lop_and_or(w, NIB_MASK, NIB_MAGIC);
+    const uint32_t a1 = lop_and_or(w >> 4, NIB_MASK, NIB_MAGIC);
+    const uint32_t a2 = lop_and_or(w >> 8, NIB_MASK, NIB_MAGIC);
+    const uint32_t a3 = lop_and_or(rotr(w, 12), NIB_MASK, NIB_MAGIC);
+    mma_bf16_16816(a, a0, a1, a2, a3, b0, b1);
+  };
 
-  int it = i0 + warp, vt = 0, gk = 0;
-  if (it < i1) {
-    vt = it / G;
-    gk = it - vt * G;
-  }
+  int it = i0 + warp * BPW;  // first item of this warp in the current chunk
+  int vt = it / G, gk = it - vt * G;
   int slot = 0;
   uint32_t phase = 0;
   for (int ch = 0; ch < nch; ++ch) {
-    mbar_wait(&full[slot], phase);
-    if (it < i1) {
-      if (vt != cur_vt) {
-        if (cur_vt >= 0) flush(cur_vt);
-        cur_vt = vt;
-        out[0] = out[1] = out[2] = out[3] = 0.f;
-      }
-      const uint32_t blk = smem_u32(ring) + (uint32_t)(slot * CHB + warp * BLK);
-      const uint2 sz = lds64(blk + KB * 8 + g * 8);
-      const uint2 sxv = lds64(sx_lane + gk * 32);
-      const float s0 = __uint_as_float(sz.x << 16), zn0 = __uint_as_float(sz.x & 0xffff0000u);
-      const float s1 = __uint_as_float(sz.y << 16), zn1 = __uint_as_float(sz.y & 0xffff0000u);
-      const float sx0 = __uint_as_float(sxv.x), sx1 = __uint_as_float(sxv.y);
-      float accA[4] = {zn0 * sx0, zn0 * sx1, zn1 * sx0, zn1 * sx1};
-      float accB[4] = {0.f, 0.f, 0.f, 0.f};
-      const uint32_t xk = xs_lane + (uint32_t)(gk * KB * 2);
-      auto step_pair = [&](uint32_t w0, uint32_t w1, int sp) {
-        uint4 xv = make_uint4(0u, 0u, 0u, 0u);
-        if (has_x) xv = lds128(xk + sp * 64);
-        {
-          const uint32_t a0 = lop_and_or(w0, NIB_MASK, NIB_MAGIC);
-          const uint32_t a1 = lop_and_or(w0 >> 4, NIB_MASK, NIB_MAGIC);
-          const uint32_t a2 = lop_and_or(w0 >> 8, NIB_MASK, NIB_MAGIC);
-          const uint32_t a3 = lop_and_or(rotr(w0, 12), NIB_MASK, NIB_MAGIC);
-          mma_bf16_16816(accA, a0, a1, a2, a3, xv.x, xv.y);
-        }
-        {
-          const uint32_t a0 = lop_and_or(w1, NIB_MASK, NIB_MAGIC);
-          const uint32_t a1 = lop_and_or(w1 >> 4, NIB_MASK, NIB_MAGIC);
-          const uint32_t a2 = lop_and_or(w1 >> 8, NIB_MASK, NIB_MAGIC);
-          const uint32_t a3 = lop_and_or(rotr(w1, 12), NIB_MASK, NIB_MAGIC);
-          mma_bf16_16816(accB, a0, a1, a2, a3, xv.z, xv.w);
-        }
-      };
-      if constexpr (KSP == 1) {
-        const uint2 t = lds64(blk + lane * 8);
-        step_pair(t.x, t.y, 0);
-      } else {
+    mbar_wait_u32(full_u + slot * 8, phase);
+    const uint32_t blk0 = ring_u + (uint32_t)(slot * CHB);
+    float t[BPW][4];
+    uint2 sz[BPW], sxv[BPW];
+    int bvt[BPW];
+    {
+      int v2 = vt, g2 = gk;
 #pragma unroll
-        for (int h = 0; h < KSP / 2; ++h) {
-          const uint4 t = lds128(blk + h * 512 + lane * 16);
-          step_pair(t.x, t.y, 2 * h);
-          step_pair(t.z, t.w, 2 * h + 1);
+      for (int b = 0; b < BPW; ++b) {
+        bvt[b] = (it + b < i1) ? v2 : -1;
+        // blocks past the end of the range read stale ring bytes: harmless, their sums are dropped
+        const uint32_t blk = blk0 + b * BLK;
+        const int gg = (it + b < i1) ? g2 : 0;
+        sz[b] = lds64(blk + KB * 8 + g * 8);
+        sxv[b] = lds64(sx_lane + gg * 32);
+        const uint32_t xk = xs_lane + (uint32_t)(gg * KB * 2);
+        float acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[0][i] = acc[1][i] = acc[2][i] = acc[3][i] = 0.f;
+        if constexpr (KSP == 1) {
+          const uint2 wq = lds64(blk + lane * 8);
+          const uint4 xv = lds128(xk);
+          mma_word(acc[0], wq.x, xv.x, xv.y);
+          mma_word(acc[1], wq.y, xv.z, xv.w);
+        } else {
+#pragma unroll
+          for (int h = 0; h < KSP / 2; ++h) {
+            const uint4 wq = lds128(blk + h * 512 + lane * 16);
+            const uint4 xa = lds128(xk + (2 * h) * 64);
+            const uint4 xb = lds128(xk + (2 * h + 1) * 64);
+            mma_word(acc[0], wq.x, xa.x, xa.y);
+            mma_word(acc[1], wq.y, xa.z, xa.w);
+            mma_word(acc[2], wq.z, xb.x, xb.y);
+            mma_word(acc[3], wq.w, xb.z, xb.w);
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) t[b][i] = (acc[0][i] + acc[1][i]) + (acc[2][i] + acc[3][i]);
+        if (++g2 == G) {
+          g2 = 0;
+          ++v2;
         }
       }
-      out[0] = fmaf(s0, accA[0] + accB[0], out[0]);
-      out[1] = fmaf(s0, accA[1] + accB[1], out[1]);
-      out[2] = fmaf(s1, accA[2] + accB[2], out[2]);
-      out[3] = fmaf(s1, accA[3] + accB[3], out[3]);
+    }
+#pragma unroll
+    for (int b = 0; b < BPW; ++b) {
+      if (bvt[b] >= 0) {
+        if (bvt[b] != cur_vt) {
+          if (cur_vt >= 0) flush(cur_vt);
+          cur_vt = bvt[b];
+          out[0] = out[1] = out[2] = out[3] = 0.f;
+        }
+        const float s0 = __uint_as_float(sz[b].x << 16), zn0 = __uint_as_float(sz[b].x & 0xffff0000u);
+        const float s1 = __uint_as_float(sz[b].y << 16), zn1 = __uint_as_float(sz[b].y & 0xffff0000u);
+        const float sx0 = __uint_as_float(sxv[b].x), sx1 = __uint_as_float(sxv[b].y);
+        // sum (16+q) x  -  (16+z) sum x  =  sum (q - z) x ; then the group scale
+        out[0] = fmaf(s0, fmaf(zn0, sx0, t[b][0]), out[0]);
+        out[1] = fmaf(s0, fmaf(zn0, sx1, t[b][1]), out[1]);
+        out[2] = fmaf(s1, fmaf(zn1, sx0, t[b][2]), out[2]);
+        out[3] = fmaf(s1, fmaf(zn1, sx1, t[b][3]), out[3]);
+      }
     }
     __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[slot]);
+    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty_u + slot * 8) : "memory");
     it += CH;
     gk += CH;
     while (gk >= G) {
@@ -327,103 +461,63 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12) ? 2 : 1) gemv_int4_ker
     }
   }
   if (cur_vt >= 0) flush(cur_vt);
+  TRACE(4);
   consumer_sync(NCONS);
 
-  // ---- cross-warp reduction (fixed warp order) into cta[slot][m][n]
-  for (int e = ctid; e < nvt * MT; e += NCONS) {
-    const int sv = e / MT, r = e - sv * MT;
-    float v = 0.f;
-#pragma unroll
-    for (int w = 0; w < W; ++w) v += red[((size_t)sv * W + w) * MT + r];
-    cta[e] = v;
-  }
-  consumer_sync(NCONS);
-
-  // ---- per tile: (cross-CTA combine) + fused epilogue, one warp per tile
-  const int nmat = p.nmat, GT = p.GT;
-  const int T_first = vt_first / nmat, T_last = vt_last / nmat;
+  TRACE(5);
+  // ---- fused epilogue, one warp per tile (every tile is complete inside its CTA)
   float* vals = wv + (size_t)warp * nmat * MT;  // [nmat][M][16]
   for (int T = T_first + warp; T <= T_last; T += W) {
-    const int c_lo = range_owner(T * GT, p.I, P), c_hi = range_owner((T + 1) * GT - 1, p.I, P);
-    const int ncontrib = c_hi - c_lo + 1;
-    // this CTA's (possibly partial) sums for the tile; zero where it holds no item of a matrix
+    const int n0 = T * TILE_N;
+    float pre[4] = {pre0[0], pre0[1], pre0[2], pre0[3]};
+    float2 cs[2] = {cs0[0], cs0[1]};
+    if (T != T_first + warp) load_pre(T, pre, cs);
+    // cross-warp reduction of this tile's sums in fixed warp order (deterministic)
     for (int e = lane; e < nmat * MT; e += 32) {
-      const int mat = e / MT, r = e - mat * MT;
-      const int vt = T * nmat + mat;
-      vals[e] = (vt >= vt_first && vt <= vt_last) ? cta[(size_t)(vt - vt_first) * MT + r] : 0.f;
+      const float* r = red + (size_t)(T * nmat - vt_first) * W * MT + (e / MT) * W * MT + (e % MT);
+      float v = 0.f;
+#pragma unroll
+      for (int w = 0; w < W; ++w) v += r[w * MT];
+      vals[e] = v;
     }
     __syncwarp();
-    bool run_epilogue = true;
-    if (ncontrib > 1) {
-      float* mine = p.partials + ((size_t)T * p.maxc + (c - c_lo)) * nmat * MT;
-      for (int e = lane; e < nmat * MT; e += 32) mine[e] = vals[e];
-      __threadfence();
-      __syncwarp();
-      int last = 0;
-      if (lane == 0) {
-        last = (atomicAdd(&p.counters[T], 1) == ncontrib - 1);
-        if (last) __threadfence();
-      }
-      last = __shfl_sync(0xffffffffu, last, 0);
-      run_epilogue = last != 0;
-      if (run_epilogue) {
-        const float* base = p.partials + (size_t)T * p.maxc * nmat * MT;
-        for (int e = lane; e < nmat * MT; e += 32) {
-          float v = 0.f;
-          for (int i = 0; i < ncontrib; ++i) v += __ldcg(base + (size_t)i * nmat * MT + e);
-          vals[e] = v;
-        }
-        if (lane == 0) p.counters[T] = 0;
-        __syncwarp();
-      }
-    }
-    if (!run_epilogue) continue;
-
-    const int n0 = T * TILE_N;
     if (p.epilogue == LL_EPI_STORE) {
+      const float bias = pre[0];
       for (int e = lane; e < MT; e += 32) {
         const int m = e >> 4, n = n0 + (e & 15);
-        float v = vals[e];
-        if (p.bias) v += __bfloat162float(p.bias[n]);
-        p.y[(size_t)m * p.N + n] = __float2bfloat16_rn(v);
+        p.y[(size_t)m * p.N + n] = __float2bfloat16_rn(vals[e] + bias);
       }
     } else if (p.epilogue == LL_EPI_RESIDUAL) {
-      // x = bf16(x + bf16(h)); partial sum of bf16(x*x) over this tile for the next RMSNorm
-      for (int mm = 0; mm < M; mm += 2) {
-        const int m = mm + (lane >> 4), nl = lane & 15;
-        float ss = 0.f;
-        if (m < M) {
-          const size_t o = (size_t)m * p.N + n0 + nl;
-          const float h = bf16r(vals[m * TILE_N + nl]);
-          const float xn = bf16r(__fadd_rn(__bfloat162float(p.y[o]), h));
-          p.y[o] = __float2bfloat16_rn(xn);
-          ss = bf16r(__fmul_rn(xn, xn));
+      // x = bf16(x + bf16(h))   (ref model.py:172-173)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int e = lane + 32 * j;
+        if (e < MT) {
+          const float h = bf16r(vals[e]);
+          p.y[(size_t)(e >> 4) * p.N + n0 + (e & 15)] = __float2bfloat16_rn(__fadd_rn(pre[j], h));
         }
-        ss += __shfl_xor_sync(0xffffffffu, ss, 8);
-        ss += __shfl_xor_sync(0xffffffffu, ss, 4);
-        ss += __shfl_xor_sync(0xffffffffu, ss, 2);
-        ss += __shfl_xor_sync(0xffffffffu, ss, 1);
-        if (m < M && nl == 0 && p.ssq_out) p.ssq_out[(size_t)m * p.ntiles + T] = ss;
       }
     } else if (p.epilogue == LL_EPI_ROPE_KV) {
       const int E = p.N / 3, hs = p.head_size;
-      const int rope_pos = p.pos[0], slot = p.pos[1];
-      for (int e = lane; e < M * (TILE_N / 2); e += 32) {
-        const int m = e >> 3, cc = 2 * (e & 7), n = n0 + cc;
-        const int part = n / E, ee = n - part * E, head = ee / hs, d = ee - head * hs;
-        float x0 = bf16r(vals[m * TILE_N + cc]), x1 = bf16r(vals[m * TILE_N + cc + 1]);
-        if (part < 2) {
-          const float2 cs = *reinterpret_cast<const float2*>(p.rope + ((size_t)rope_pos * (hs / 2) + d / 2) * 2);
-          const float o0 = __fsub_rn(__fmul_rn(x0, cs.x), __fmul_rn(x1, cs.y));
-          const float o1 = __fadd_rn(__fmul_rn(x1, cs.x), __fmul_rn(x0, cs.y));
-          x0 = o0; x1 = o1;
-        }
-        const __nv_bfloat162 o = __floats2bfloat162_rn(x0, x1);
-        if (part == 0) {
-          *reinterpret_cast<__nv_bfloat162*>(p.y + (size_t)m * E + ee) = o;
-        } else {
-          __nv_bfloat16* cache = part == 1 ? p.k_cache : p.v_cache;
-          *reinterpret_cast<__nv_bfloat162*>(cache + (((size_t)m * p.n_head + head) * p.cache_len + slot) * hs + d) = o;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int e = lane + 32 * j;
+        if (e < M * (TILE_N / 2)) {
+          const int m = e >> 3, cc = 2 * (e & 7), n = n0 + cc;
+          const int part = n / E, ee = n - part * E, head = ee / hs, d = ee - head * hs;
+          float x0 = bf16r(vals[m * TILE_N + cc]), x1 = bf16r(vals[m * TILE_N + cc + 1]);
+          if (part < 2) {
+            const float o0 = __fsub_rn(__fmul_rn(x0, cs[j].x), __fmul_rn(x1, cs[j].y));
+            const float o1 = __fadd_rn(__fmul_rn(x1, cs[j].x), __fmul_rn(x0, cs[j].y));
+            x0 = o0; x1 = o1;
+          }
+          const __nv_bfloat162 o = __floats2bfloat162_rn(x0, x1);
+          if (part == 0) {
+            *reinterpret_cast<__nv_bfloat162*>(p.y + (size_t)m * E + ee) = o;
+          } else {
+            __nv_bfloat16* cache = part == 1 ? p.k_cache : p.v_cache;
+            *reinterpret_cast<__nv_bfloat162*>(cache + (((size_t)m * p.n_head + head) * p.cache_len + kv_slot) * hs + d) = o;
+          }
         }
       }
     } else {  // LL_EPI_SWIGLU
@@ -436,6 +530,7 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12) ? 2 : 1) gemv_int4_ker
     }
     __syncwarp();
   }
+  TRACE(6);
 }
 
 // ------------------------------------------------------------------------------------ repack
@@ -493,21 +588,39 @@ __global__ void int4_repack_kernel(const uint8_t* __restrict__ qw, const P* __re
 
 // ------------------------------------------------------------------------------------ host side
 struct Plan {
-  int KB, KSP, BLK, W;
+  int KB, KSP, BLK, W, BPW;
   int G, GT, ntiles, I, P;
-  int maxc, ts_max, S;
-  int xs_stride, off_xs, off_sx, off_red, off_cta, off_wv, off_bar;
+  int ts_max, S;
+  int xs_stride, off_xs, off_sx, off_red, off_wv, off_bar, off_nw;
   size_t smem;
 };
+
+unsigned long long* g_trace = nullptr;  // debug: device buffer [launches][256][8]
+int g_trace_launches = 0, g_trace_idx = 0;
 
 constexpr int SMEM_CORESIDENT = 110 * 1024;  // two such CTAs (this GEMV + the next one, under PDL) fit one SM
 constexpr int SMEM_SOLO = 220 * 1024;
 constexpr int MAX_SLOTS = 12;
 
-int consumer_warps(int M) { return M <= 2 ? 12 : (M <= 4 ? 8 : 4); }
+// consumer warps x blocks per warp per chunk; LLB200_GEMV_CFG="WxB" overrides the M <= 2 default (tuning)
+void consumer_config(int M, int KSP, int* W, int* BPW) {
+  static int env_w = -1, env_b = -1;
+  if (env_w < 0) {
+    env_w = 0; env_b = 0;
+    if (const char* e = getenv("LLB200_GEMV_CFG")) {
+      int w = 0, b = 0;
+      if (sscanf(e, "%dx%d", &w, &b) == 2 && (w == 4 || w == 8 || w == 12 || w == 16) && (b == 1 || b == 2)) {
+        env_w = w; env_b = b;
+      }
+    }
+  }
+  // measured on the 7B decode chain (profiles/r01_step_probe.md): 8 warps x 2 blocks beats 12 x 1 by 6 %
+  if (M <= 2) { *W = 8; *BPW = KSP == 4 ? 2 : 1; } else if (M <= 4) { *W = 8; *BPW = 1; } else { *W = 4; *BPW = 1; }
+  if (M <= 2 && KSP == 4 && env_w > 0) { *W = env_w; *BPW = env_b; }
+}
 
 // Fills `pl`; returns LL_OK, or LL_ERR_UNSUPPORTED with a message when the shape does not fit.
-int make_plan(int N, int K, int group, int nmat, int M, int grid, Plan* pl) {
+int make_plan(int N, int K, int group, int nmat, int M, int grid, bool has_norm, Plan* pl) {
   const int KB = pick_kb(K, group);
   if (KB == 0 || N % TILE_N != 0 || K % 8 != 0) {
     set_error("int4 GEMV needs N %% 16 == 0, K %% group == 0 and group %% 32 == 0 (N=%d K=%d group=%d)", N, K, group);
@@ -519,7 +632,8 @@ int make_plan(int N, int K, int group, int nmat, int M, int grid, Plan* pl) {
     return LL_ERR_CUDA;
   }
   Plan& q = *pl;
-  q.KB = KB; q.KSP = KB / 32; q.BLK = block_bytes(KB); q.W = consumer_warps(M);
+  q.KB = KB; q.KSP = KB / 32; q.BLK = block_bytes(KB);
+  consumer_config(M, q.KSP, &q.W, &q.BPW);
   q.G = K / KB; q.GT = nmat * q.G; q.ntiles = N / TILE_N;
   const long long items = (long long)q.ntiles * q.GT;
   if (items > 0x3fffffff) {
@@ -528,22 +642,23 @@ int make_plan(int N, int K, int group, int nmat, int M, int grid, Plan* pl) {
   }
   q.I = (int)items;
   q.P = grid > 0 ? grid : sms;
-  if (q.P > q.I) q.P = q.I;
-  const int ipc_min = q.I / q.P, ipc_max = (q.I + q.P - 1) / q.P;
-  q.maxc = (q.GT + ipc_min - 1) / ipc_min + 1;
-  q.ts_max = (ipc_max + q.G - 2) / q.G + 2;
+  if (q.P > q.ntiles) q.P = q.ntiles;  // whole tiles per CTA
+  const int tiles_max = (q.ntiles + q.P - 1) / q.P;
+  const int ipc_max = tiles_max * q.GT;
+  q.ts_max = tiles_max * nmat;
   const int MT = M * TILE_N;
   q.xs_stride = K * 2 + 64;
   size_t fixed = 0;
   auto take = [&](size_t bytes) { size_t o = fixed; fixed += (bytes + 127) & ~(size_t)127; return (int)o; };
-  q.off_xs = take((size_t)M * q.xs_stride);
+  q.off_xs = take((size_t)(M + 1) * q.xs_stride);
   q.off_sx = take((size_t)q.G * 8 * 4);
   q.off_red = take((size_t)q.ts_max * q.W * MT * 4);
-  q.off_cta = take((size_t)q.ts_max * MT * 4);
   q.off_wv = take((size_t)q.W * nmat * MT * 4);
-  q.off_bar = take((size_t)2 * MAX_SLOTS * 8);
-  const size_t chb = (size_t)q.W * q.BLK;
-  const int nch_max = (ipc_max + q.W - 1) / q.W;
+  q.off_bar = take((size_t)(2 * MAX_SLOTS + 2) * 8);
+  q.off_nw = take(has_norm ? (size_t)K * 2 : 0);
+  const int ch = q.W * q.BPW;
+  const size_t chb = (size_t)ch * q.BLK;
+  const int nch_max = (ipc_max + ch - 1) / ch;
   long s = ((long)SMEM_CORESIDENT - (long)fixed) / (long)chb;
   if (s < 3 && nch_max > s) s = ((long)SMEM_SOLO - (long)fixed) / (long)chb;
   if (s > MAX_SLOTS) s = MAX_SLOTS;
@@ -554,29 +669,33 @@ int make_plan(int N, int K, int group, int nmat, int M, int grid, Plan* pl) {
   }
   q.S = (int)s;
   const size_t ring = (size_t)q.S * chb;
-  q.off_xs += (int)ring; q.off_sx += (int)ring; q.off_red += (int)ring; q.off_cta += (int)ring;
-  q.off_wv += (int)ring; q.off_bar += (int)ring;
+  q.off_xs += (int)ring; q.off_sx += (int)ring; q.off_red += (int)ring;
+  q.off_wv += (int)ring; q.off_bar += (int)ring; q.off_nw += (int)ring;
   q.smem = ring + fixed;
   return LL_OK;
 }
 
-template <int W, int KSP>
+template <int W, int KSP, int BPW>
 int launch_cfg(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
   static size_t configured = 0;
   if (pl.smem > configured) {
-    if (configured == 0) prefer_max_smem(gemv_int4_kernel<W, KSP>);
-    LL_CUDA(cudaFuncSetAttribute(gemv_int4_kernel<W, KSP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+    if (configured == 0) prefer_max_smem(gemv_int4_kernel<W, KSP, BPW>);
+    LL_CUDA(cudaFuncSetAttribute(gemv_int4_kernel<W, KSP, BPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
     configured = pl.smem;
   }
-  LL_CUDA(launch(gemv_int4_kernel<W, KSP>, dim3(pl.P), dim3((W + 1) * 32), pl.smem, st, pdl, p));
+  LL_CUDA(launch(gemv_int4_kernel<W, KSP, BPW>, dim3(pl.P), dim3((W + 1) * 32), pl.smem, st, pdl, p));
   return LL_OK;
 }
 
-template <int W>
-int launch_w(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
-  if (pl.KSP == 4) return launch_cfg<W, 4>(p, pl, pdl, st);
-  if (pl.KSP == 2) return launch_cfg<W, 2>(p, pl, pdl, st);
-  return launch_cfg<W, 1>(p, pl, pdl, st);
+int launch_plan(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
+#define CFG(w, k, b) \
+  if (pl.W == w && pl.KSP == k && pl.BPW == b) return launch_cfg<w, k, b>(p, pl, pdl, st)
+  CFG(12, 4, 1); CFG(8, 4, 2); CFG(12, 4, 2); CFG(8, 4, 1); CFG(16, 4, 1); CFG(16, 4, 2); CFG(4, 4, 1); CFG(4, 4, 2);
+  CFG(12, 2, 1); CFG(8, 2, 1); CFG(4, 2, 1);
+  CFG(12, 1, 1); CFG(8, 1, 1); CFG(4, 1, 1);
+#undef CFG
+  set_error("int4 GEMV: no kernel for W=%d KSP=%d BPW=%d", pl.W, pl.KSP, pl.BPW);
+  return LL_ERR_UNSUPPORTED;
 }
 
 }  // namespace
@@ -615,12 +734,17 @@ int ll_int4_prepare(const uint8_t* qw, const void* scales, const void* zeros, in
   return LL_OK;
 }
 
-int ll_int4_gemv_plan(int N, int K, int group, int nmat, int M, int grid, size_t* partial_bytes, size_t* counter_bytes) {
+/* debug (not in the public header): stage time stamps of the next `launches` GEMV launches */
+__attribute__((visibility("default"))) void ll_debug_gemv_trace(unsigned long long* buf, int launches) {
+  g_trace = buf; g_trace_launches = launches; g_trace_idx = 0;
+}
+
+int ll_int4_gemv_plan(int N, int K, int group, int nmat, int M, int grid, size_t* smem_bytes, int32_t* ctas) {
   LL_CHECK_ARG(N > 0 && K > 0 && group > 0 && (nmat == 1 || nmat == 2) && M >= 1 && M <= MAXM, "bad plan arguments");
   Plan pl;
-  if (int r = make_plan(N, K, group, nmat, M, grid, &pl)) return r;
-  if (partial_bytes) *partial_bytes = (size_t)pl.ntiles * pl.maxc * nmat * M * TILE_N * sizeof(float);
-  if (counter_bytes) *counter_bytes = (size_t)pl.ntiles * sizeof(int32_t);
+  if (int r = make_plan(N, K, group, nmat, M, grid, true, &pl)) return r;
+  if (smem_bytes) *smem_bytes = pl.smem;
+  if (ctas) *ctas = pl.P;
   return LL_OK;
 }
 
@@ -635,7 +759,6 @@ int ll_int4_gemv(const ll_gemv_args* a, ll_stream stream) {
   LL_CHECK_ARG(((uintptr_t)a->w & 15) == 0 && ((uintptr_t)a->w2 & 15) == 0 && ((uintptr_t)a->x & 15) == 0,
                "w/w2/x must be 16-byte aligned");
   if (a->norm_weight) {
-    LL_CHECK_ARG(a->ssq && a->ssq_parts > 0, "fused RMSNorm needs ssq partials");
     LL_CHECK_ARG(((uintptr_t)a->norm_weight & 15) == 0, "norm_weight must be 16-byte aligned");
   }
   if (a->epilogue == LL_EPI_ROPE_KV) {
@@ -644,8 +767,7 @@ int ll_int4_gemv(const ll_gemv_args* a, ll_stream stream) {
                  "ROPE_KV: N must be 3*n_head*head_size");
   }
   Plan pl;
-  if (int r = make_plan(a->N, a->K, a->group, nmat, a->M, a->grid, &pl)) return r;
-  if (pl.maxc > 0 && pl.P > 1) LL_CHECK_ARG(a->partials && a->counters, "multi-CTA launch needs partials and counters scratch");
+  if (int r = make_plan(a->N, a->K, a->group, nmat, a->M, a->grid, a->norm_weight != nullptr, &pl)) return r;
 
   Params p;
   memset(&p, 0, sizeof(p));
@@ -654,24 +776,28 @@ int ll_int4_gemv(const ll_gemv_args* a, ll_stream stream) {
   p.G = pl.G; p.GT = pl.GT; p.ntiles = pl.ntiles; p.I = pl.I;
   p.x = (const __nv_bfloat16*)a->x;
   p.norm_w = (const __nv_bfloat16*)a->norm_weight;
-  p.ssq = a->ssq; p.ssq_parts = a->ssq_parts; p.eps = a->eps;
+  p.eps = a->eps;
   p.epilogue = a->epilogue;
   p.y = (__nv_bfloat16*)a->y;
   p.bias = (const __nv_bfloat16*)a->bias;
-  p.ssq_out = a->ssq_out;
   p.rope = a->rope; p.pos = a->pos;
   p.k_cache = (__nv_bfloat16*)a->k_cache; p.v_cache = (__nv_bfloat16*)a->v_cache;
   p.n_head = a->n_head; p.head_size = a->head_size; p.cache_len = a->cache_len;
-  p.partials = a->partials; p.counters = a->counters; p.maxc = pl.maxc;
+  
   p.S = pl.S; p.xs_stride = pl.xs_stride; p.ts_max = pl.ts_max;
-  p.off_xs = pl.off_xs; p.off_sx = pl.off_sx; p.off_red = pl.off_red; p.off_cta = pl.off_cta;
-  p.off_wv = pl.off_wv; p.off_bar = pl.off_bar;
+  p.off_xs = pl.off_xs; p.off_sx = pl.off_sx; p.off_red = pl.off_red;
+  p.off_wv = pl.off_wv; p.off_bar = pl.off_bar; p.off_nw = pl.off_nw;
 
+  if (g_trace != nullptr && g_trace_idx < g_trace_launches && pl.P <= 256) p.trace = g_trace + (size_t)(g_trace_idx++) * 256 * 16;
   cudaStream_t st = (cudaStream_t)stream;
   const bool pdl = (a->flags & LL_GEMV_PDL) != 0;
-  if (pl.W == 12) return launch_w<12>(p, pl, pdl, st);
-  if (pl.W == 8) return launch_w<8>(p, pl, pdl, st);
-  return launch_w<4>(p, pl, pdl, st);
+  static int delay_ns = -1;
+  if (delay_ns < 0) {
+    const char* e = getenv("LLB200_GEMV_DELAY_NS");
+    delay_ns = e ? atoi(e) : 0;
+  }
+  p.prefetch_delay_ns = pdl ? delay_ns : 0;
+  return launch_plan(p, pl, pdl, st);
 }
 
 }  // extern "C"

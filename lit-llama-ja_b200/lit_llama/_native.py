@@ -33,12 +33,12 @@ class GemvArgs(C.Structure):
     _fields_ = [
         ("w", vp), ("w2", vp),
         ("N", C.c_int32), ("K", C.c_int32), ("group", C.c_int32), ("M", C.c_int32),
-        ("x", vp), ("norm_weight", vp), ("ssq", vp), ("ssq_parts", C.c_int32), ("eps", C.c_float),
+        ("x", vp), ("norm_weight", vp), ("eps", C.c_float),
         ("epilogue", C.c_int32), ("flags", C.c_int32),
-        ("y", vp), ("bias", vp), ("ssq_out", vp),
+        ("y", vp), ("bias", vp),
         ("rope", vp), ("pos", vp), ("k_cache", vp), ("v_cache", vp),
         ("n_head", C.c_int32), ("head_size", C.c_int32), ("cache_len", C.c_int32),
-        ("partials", vp), ("counters", vp), ("grid", C.c_int32),
+        ("grid", C.c_int32),
     ]
 
 
@@ -59,7 +59,7 @@ EXPORTS = {
     "ll_qlinear_simt": ([vp, i32, i32, vp, vp, vp, i32, vp, vp, i32, i32, i32, i32, vp], C.c_int),
     "ll_int4_stream_bytes": ([i32, i32, i32], sz_t),
     "ll_int4_prepare": ([vp, vp, vp, i32, vp, i32, i32, i32, vp, vp], C.c_int),
-    "ll_int4_gemv_plan": ([i32, i32, i32, i32, i32, i32, C.POINTER(sz_t), C.POINTER(sz_t)], C.c_int),
+    "ll_int4_gemv_plan": ([i32, i32, i32, i32, i32, i32, C.POINTER(sz_t), C.POINTER(C.c_int32)], C.c_int),
     "ll_int4_gemv": ([C.POINTER(GemvArgs), vp], C.c_int),
     "ll_rmsnorm": ([vp, vp, vp, i32, i32, i32, C.c_float, vp], C.c_int),
     "ll_embed_ssq": ([vp, vp, vp, vp, i32, i32, vp], C.c_int),
@@ -74,7 +74,7 @@ EXPORTS = {
 }
 _fn = {name: _proto(name, a, r) for name, (a, r) in EXPORTS.items()}
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 if _fn["ll_abi_version"]() != ABI_VERSION:
     raise ImportError("libllb200.so ABI version mismatch; rebuild with lit-llama-ja_b200/build.py")
 
@@ -122,10 +122,10 @@ def stream() -> C.c_void_p:
 
 
 def gemv_plan(N: int, K: int, group: int, nmat: int, M: int, grid: int = 0):
-    """(partial_bytes, counter_bytes) of scratch the GEMV needs; raises if the shape is unsupported."""
-    pb, cb = sz_t(), sz_t()
-    check(_fn["ll_int4_gemv_plan"](N, K, group, nmat, M, grid, C.byref(pb), C.byref(cb)), "ll_int4_gemv_plan")
-    return pb.value, cb.value
+    """(shared-memory bytes, CTAs) of the launch the GEMV would use; raises if the shape is unsupported."""
+    sm, ctas = sz_t(), C.c_int32()
+    check(_fn["ll_int4_gemv_plan"](N, K, group, nmat, M, grid, C.byref(sm), C.byref(ctas)), "ll_int4_gemv_plan")
+    return sm.value, ctas.value
 
 
 def gemv_supported(N: int, K: int, group: int, nmat: int, M: int) -> bool:
@@ -147,16 +147,13 @@ def attn_scratch_bytes(B, n_head, hs, splits) -> int:
 
 
 class Workspace:
-    """Per-(device, stream) scratch for split-K partial sums, arrival counters and the
-    attention split states.  Kernels on one stream are ordered, so one buffer is shared by
-    every layer; counters are zeroed once and the kernels leave them zero."""
+    """Per-(device, stream) scratch for the attention split states.  Kernels on one stream are ordered,
+    so one buffer is shared by every layer; counters are zeroed once and the kernels leave them zero."""
 
     _cache: dict = {}
 
     def __init__(self, device):
         self.device = device
-        self.partials = torch.empty(1 << 20, dtype=torch.float32, device=device)
-        self.counters = torch.zeros(1024, dtype=torch.int32, device=device)
         self.attn_scratch = torch.empty(1 << 18, dtype=torch.float32, device=device)
         self.attn_counters = torch.zeros(4096, dtype=torch.int32, device=device)
 
@@ -169,11 +166,7 @@ class Workspace:
             ws = cls._cache[key] = Workspace(device)
         return ws
 
-    def ensure(self, partial_bytes=0, counter_bytes=0, attn_bytes=0, attn_counters=0):
-        if partial_bytes > self.partials.numel() * 4:
-            self.partials = torch.empty(partial_bytes // 4 + 1, dtype=torch.float32, device=self.device)
-        if counter_bytes > self.counters.numel() * 4:
-            self.counters = torch.zeros(counter_bytes // 4 + 1, dtype=torch.int32, device=self.device)
+    def ensure(self, attn_bytes=0, attn_counters=0):
         if attn_bytes > self.attn_scratch.numel() * 4:
             self.attn_scratch = torch.empty(attn_bytes // 4 + 1, dtype=torch.float32, device=self.device)
         if attn_counters > self.attn_counters.numel():

@@ -3,13 +3,13 @@
 One decode step = 1 embedding kernel + 5 kernels per block + 1 lm_head kernel, all launched with
 programmatic dependent launch so each GEMV's TMA weight stream starts while its predecessor drains:
 
-    embed_ssq                                    wte row + sum-of-squares partials
+    embed                                        wte row
     per block:
       gemv c_attn   [RMSNorm prologue | RoPE + KV-cache write epilogue]      (ref model.py:204-228)
       decode_attn   split-KV, deterministic combine                          (ref model.py:237)
-      gemv c_proj   [residual-add epilogue + ssq partials]                   (ref model.py:172, 242)
+      gemv c_proj   [residual-add epilogue]                                  (ref model.py:172, 242)
       gemv c_fc1|c_fc2 [RMSNorm prologue | SwiGLU epilogue]                  (ref model.py:258)
-      gemv mlp.c_proj  [residual-add epilogue + ssq partials]                (ref model.py:173, 259)
+      gemv mlp.c_proj  [residual-add epilogue]                               (ref model.py:173, 259)
     gemv lm_head    [RMSNorm (ln_f) prologue]                                (ref model.py:125-127)
 
 Positions live in a device int32[3] (pos, ring slot, #valid slots) that ``ll_set_pos`` /
@@ -65,12 +65,10 @@ class DecodeEngine:
         self.model, self.B, self.S = model, B, max_seq_length
         dev = model.transformer.wte.weight.device
         E, H, V = cfg.n_embd, cfg.n_hidden, cfg.padded_vocab_size
-        self.nparts = E // 16
         bf, f32, i32 = torch.bfloat16, torch.float32, torch.int32
         self.tok = torch.zeros(B, dtype=torch.int64, device=dev)
         self.pos = torch.zeros(3, dtype=i32, device=dev)
         self.x = torch.zeros((B, E), dtype=bf, device=dev)        # residual stream
-        self.ssq = torch.zeros((B, self.nparts), dtype=f32, device=dev)
         self.q = torch.zeros((B, E), dtype=bf, device=dev)
         self.att = torch.zeros((B, E), dtype=bf, device=dev)
         self.h = torch.zeros((B, H), dtype=bf, device=dev)
@@ -84,19 +82,6 @@ class DecodeEngine:
         self.n_launches = 0
         self.n_replays = 0
 
-        # split plans + scratch (owned by the engine: nothing is allocated during capture)
-        pb_max, cb_max = 0, 0
-        for name, (n, k, g, nmat) in {
-            "attn": (3 * E, E, model.transformer.h[0].attn.c_attn.tile_cols, 1),
-            "proj": (E, E, model.transformer.h[0].attn.c_proj.tile_cols, 1),
-            "fc": (H, E, model.transformer.h[0].mlp.c_fc1.tile_cols, 2),
-            "down": (E, H, model.transformer.h[0].mlp.c_proj.tile_cols, 1),
-            "head": (V, E, model.lm_head.tile_cols, 1),
-        }.items():
-            pb, cb = N.gemv_plan(n, k, g, nmat, B)
-            pb_max, cb_max = max(pb_max, pb), max(cb_max, cb)
-        self.partials = torch.empty(pb_max // 4 + 16, dtype=f32, device=dev)
-        self.counters = torch.zeros(cb_max // 4 + 16, dtype=i32, device=dev)
         nh, hs = cfg.n_head, cfg.head_size
         self.splits = max(1, min(16, (2 * N._fn["ll_sm_count"]()) // max(1, B * nh), (max_seq_length + 63) // 64))
         self.attn_scratch = torch.empty(N.attn_scratch_bytes(B, nh, hs, self.splits) // 4 + 16, dtype=f32, device=dev)
@@ -126,11 +111,8 @@ class DecodeEngine:
         a.N, a.K, a.group, a.M = lin.out_features, lin.in_features, lin.tile_cols, self.B
         a.x, a.y = x.data_ptr(), y.data_ptr()
         if norm is not None:
-            a.norm_weight, a.ssq, a.ssq_parts, a.eps = norm.scale.data_ptr(), self.ssq.data_ptr(), self.nparts, norm.eps
-        a.epilogue, a.flags = epi, (N.GEMV_PDL if self.use_pdl else 0)
-        if epi == N.EPI_RESIDUAL:
-            a.ssq_out = self.ssq.data_ptr()
-        a.partials, a.counters, a.grid = self.partials.data_ptr(), self.counters.data_ptr(), 0
+            a.norm_weight, a.eps = norm.scale.data_ptr(), norm.eps
+        a.epilogue, a.flags, a.grid = epi, (N.GEMV_PDL if self.use_pdl else 0), 0
         return a
 
     def _build_args(self):
@@ -155,7 +137,7 @@ class DecodeEngine:
         cfg = self.model.config
         st = N.stream()
         wte = self.model.transformer.wte.weight
-        N.call("ll_embed_ssq", N.ptr(wte), N.ptr(self.tok), N.ptr(self.x), N.ptr(self.ssq), self.B, cfg.n_embd, st)
+        N.call("ll_embed_ssq", N.ptr(wte), N.ptr(self.tok), N.ptr(self.x), None, self.B, cfg.n_embd, st)
         flags = N.GEMV_PDL if (self.use_pdl and self.attn_pdl) else 0
         n = 1
         for a_attn, kc, vc, a_proj, a_fc, a_down in self.layers:

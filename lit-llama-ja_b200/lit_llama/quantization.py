@@ -164,17 +164,12 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         return y.reshape(out_shape)
 
     def _gemv(self, x, y, *, pdl=False, grid=0):
-        ws = N.Workspace.get(x.device)
-        M = x.shape[0]
-        pb, cb = N.gemv_plan(self.out_features, self.in_features, self.tile_cols, 1, M, grid)
-        ws.ensure(pb, cb)
         a = N.GemvArgs()
         a.w = self._stream.data_ptr()
-        a.N, a.K, a.group, a.M = self.out_features, self.in_features, self.tile_cols, M
+        a.N, a.K, a.group, a.M = self.out_features, self.in_features, self.tile_cols, x.shape[0]
         a.x, a.y = x.data_ptr(), y.data_ptr()
         a.bias = 0 if self.bias is None else self.bias.data_ptr()
-        a.epilogue, a.flags = N.EPI_STORE, (N.GEMV_PDL if pdl else 0)
-        a.partials, a.counters, a.grid = ws.partials.data_ptr(), ws.counters.data_ptr(), grid
+        a.epilogue, a.flags, a.grid = N.EPI_STORE, (N.GEMV_PDL if pdl else 0), grid
         N.gemv(a)
 
 

@@ -40,7 +40,7 @@ def timed_graph(fn, reps=20):
     return 1e3 * e0.elapsed_time(e1) / reps
 
 
-for pdl, apdl in ((True, True), (True, False), (False, False)):
+for pdl, apdl in ((True, False),):
     os.environ["LLB200_PDL"] = "1" if pdl else "0"
     os.environ["LLB200_PDL_ATTN"] = "1" if apdl else "0"
     model.kv_caches.clear(); model._engine = None
@@ -72,5 +72,5 @@ for pdl, apdl in ((True, True), (True, False), (False, False)):
                         NV.gemv(layer[{"q": 0, "p": 3, "f": 4, "d": 5}[c]])
         return f
 
-    parts = {sp: timed_graph(seq(sp)) for sp in ("q", "A", "p", "f", "d", "qA", "Ap", "qAp", "qp", "pf", "fd", "dq", "qpfd", "qApfd", "pfdq")}
-    print(f"PDL={pdl} attnPDL={apdl}: full {timed_graph(eng._run_step):7.1f} | " + " ".join(f"{k}={v:.0f}" for k, v in parts.items()), flush=True)
+    parts = {sp: timed_graph(seq(sp)) for sp in os.environ.get("PROBE_SEQS", "q,A,p,f,d,qpfd,qApfd").split(",")}
+    print(f"cfg={os.environ.get('LLB200_GEMV_CFG', 'default')} PDL={pdl} attnPDL={apdl}: full {timed_graph(eng._run_step):7.1f} | " + " ".join(f"{k}={v:.0f}" for k, v in parts.items()), flush=True)

@@ -176,21 +176,20 @@ def test_int4_gemv_vs_oracle(N, K, tile, M):
 
 
 def test_int4_gemv_forced_grid_matches():
-    """Any CTA count gives the same result up to fp32 summation order; counters are left zero."""
-    from lit_llama import _native as NV
-
+    """Any CTA count gives the same bits: a tile is summed inside one CTA in a fixed order."""
     N_, K, tile = 512, 2048, 128
     packed, s, z = _bf16_layer(N_, K, tile, 5)
     lin = make_lin(N_, K, 4, tile, s, z, "bf16", packed)
     lin.prepare()
     xn = OQ.bf16_round(np.random.RandomState(2).randn(2, K).astype(np.float32))
     x = torch.from_numpy(xn).to(DEV, torch.bfloat16)
+    outs = []
     for grid in (1, 2, 3, 7, 32, 100, 148, 512):
         y = torch.empty((2, N_), device=DEV, dtype=torch.bfloat16)
         lin._gemv(x, y, grid=grid)
-        ws = NV.Workspace.get(x.device)
-        assert int(ws.counters.abs().sum()) == 0  # counters are left zero
-        exact_close(y.float().cpu().numpy(), xn, packed, s, z, tile)
+        outs.append(y.float().cpu().numpy())
+        exact_close(outs[-1], xn, packed, s, z, tile)
+    assert all(np.array_equal(outs[0], o) for o in outs[1:])
 
 
 def test_simt_linear_fp32_8bit_and_bias():
