@@ -134,6 +134,15 @@ LL_API int ll_int4_gemv_plan(int N, int K, int group, int nmat, int M, int grid,
 LL_API int ll_int4_gemv(const ll_gemv_args* args /* host */, ll_stream stream);
 
 /* ---------------------------------------------------------------------------------------
+ * Large-M path (prefill, batched decode): tcgen05 / TMEM / TMA tensor-core GEMM.
+ * y[M][N] = x[M][K] . w[N][K]^T (+ bias), all bf16 row-major, fp32 accumulation in TMEM.  With
+ * w = ll_get_weight(..., LL_BF16) this is the reference's F.linear(inp, get_weight(inp.dtype), bias)
+ * (quantization.py:420-421) and what its Triton kernel (quantization.py:185-331) computes for large M.
+ * K % 8 == 0; any M, N (tails are zero-filled by TMA and masked on store).
+ * ------------------------------------------------------------------------------------- */
+LL_API int ll_gemm_bf16_tc(const void* x, const void* w, const void* bias, void* y, int M, int N, int K, ll_stream stream);
+
+/* ---------------------------------------------------------------------------------------
  * model.py kernels
  * ------------------------------------------------------------------------------------- */
 

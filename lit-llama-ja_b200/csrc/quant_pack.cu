@@ -90,6 +90,39 @@ __global__ void get_weight_kernel(const uint8_t* __restrict__ qw, const P* __res
   }
 }
 
+// ---------------------------------------------------------------- unpack, int4 -> bf16 fast path
+// Same arithmetic as get_weight_kernel (bit-exact get_weight(dtype=bf16)); tile = 64 columns x 128 k staged
+// through shared memory, 16-byte coalesced loads of the packed rows and 64 contiguous bytes stored per thread.
+template <typename P>
+__global__ void __launch_bounds__(256) get_weight_int4_bf16_kernel(const uint8_t* __restrict__ qw, const P* __restrict__ scales,
+                                                                   const P* __restrict__ zeros, __nv_bfloat16* __restrict__ out,
+                                                                   int N, int K, int tile, int G) {
+  __shared__ __align__(16) uint8_t raw[64][80];  // [packed row][column], 16 B of padding per row
+  const int n0 = blockIdx.x * 64, k0 = blockIdx.y * 128;
+  {
+    const int r = threadIdx.x >> 2, seg = threadIdx.x & 3;  // 64 packed rows x 4 segments of 16 columns
+    const uint4 v = *reinterpret_cast<const uint4*>(qw + (size_t)(k0 / 2 + r) * N + n0 + seg * 16);
+    *reinterpret_cast<uint4*>(&raw[r][seg * 16]) = v;
+  }
+  __syncthreads();
+  const int nl = threadIdx.x & 63, kq = threadIdx.x >> 6;  // column, quarter of the k range (32 k = 16 packed rows)
+  const int n = n0 + nl, kb = k0 + kq * 32;
+  const int g = kb / tile;
+  const float s = dt<P>::ld(scales, (size_t)n * G + g);
+  const float z = dt<P>::ld(zeros, (size_t)n * G + g);
+  uint32_t o[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const uint32_t b = raw[kq * 16 + i][nl];
+    const float lo = bf16r(__fmul_rn(bf16r(__fsub_rn((float)(b & 15u), z)), s));
+    const float hi = bf16r(__fmul_rn(bf16r(__fsub_rn((float)(b >> 4), z)), s));
+    o[i] = (uint32_t)f32_to_bf16_bits(lo) | ((uint32_t)f32_to_bf16_bits(hi) << 16);
+  }
+  uint4* dst = reinterpret_cast<uint4*>(out + (size_t)n * K + kb);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) dst[i] = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+}
+
 // ---------------------------------------------------------------- reference-semantics linear (row F)
 // Block = 32 columns x 8 k-lanes; up to 8 rows of x per pass.  fp32 accumulation.
 template <typename A, typename P>
@@ -190,9 +223,19 @@ int ll_get_weight(const uint8_t* qw, const void* scales, const void* zeros, int 
   int tile, G;
   if (int r = check_quant_args(N, K, bits, tile_cols, &tile, &G)) return r;
   LL_CHECK_ARG(qw && scales && zeros && out, "null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (bits == 4 && odt == LL_BF16 && N % 64 == 0 && K % 128 == 0 && tile % 32 == 0 && K / 128 <= 65535 &&
+      ((uintptr_t)qw & 15) == 0 && ((uintptr_t)out & 15) == 0 && (pdt == LL_BF16 || pdt == LL_F32)) {
+    dim3 fgrid(N / 64, K / 128);
+    if (pdt == LL_BF16)
+      get_weight_int4_bf16_kernel<__nv_bfloat16><<<fgrid, 256, 0, st>>>(qw, (const __nv_bfloat16*)scales, (const __nv_bfloat16*)zeros, (__nv_bfloat16*)out, N, K, tile, G);
+    else
+      get_weight_int4_bf16_kernel<float><<<fgrid, 256, 0, st>>>(qw, (const float*)scales, (const float*)zeros, (__nv_bfloat16*)out, N, K, tile, G);
+    LL_LAUNCH_OK("get_weight_int4_bf16_kernel");
+    return LL_OK;
+  }
   dim3 block(32, 8), grid((N + 31) / 32, (K + 31) / 32);
   LL_CHECK_ARG(grid.y <= 65535, "K too large for this kernel (%d)", K);
-  cudaStream_t st = (cudaStream_t)stream;
 #define GETW(OT, PT) get_weight_kernel<OT, PT><<<grid, block, 0, st>>>(qw, (const PT*)scales, (const PT*)zeros, (OT*)out, N, K, bits, tile, G)
   if (odt == LL_F32 && pdt == LL_F32) GETW(float, float);
   else if (odt == LL_F32 && pdt == LL_BF16) GETW(float, __nv_bfloat16);

@@ -61,6 +61,7 @@ EXPORTS = {
     "ll_int4_prepare": ([vp, vp, vp, i32, vp, i32, i32, i32, vp, vp], C.c_int),
     "ll_int4_gemv_plan": ([i32, i32, i32, i32, i32, i32, C.POINTER(sz_t), C.POINTER(C.c_int32)], C.c_int),
     "ll_int4_gemv": ([C.POINTER(GemvArgs), vp], C.c_int),
+    "ll_gemm_bf16_tc": ([vp, vp, vp, vp, i32, i32, i32, vp], C.c_int),
     "ll_rmsnorm": ([vp, vp, vp, i32, i32, i32, C.c_float, vp], C.c_int),
     "ll_embed_ssq": ([vp, vp, vp, vp, i32, i32, vp], C.c_int),
     "ll_rope_kv_append": ([vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp], C.c_int),

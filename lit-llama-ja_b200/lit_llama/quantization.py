@@ -174,11 +174,17 @@ class ColBlockQuantizedLinear(torch.nn.Module):
 
 
 def dequant_gemm(lin: ColBlockQuantizedLinear, x: torch.Tensor) -> torch.Tensor:
-    """Large-M path (prefill): materialise W in the activation dtype with the bit-exact unpack
-    kernel and run the dense GEMM - exactly the reference's fallback branch (quantization.py:420-421).
-    The dense GEMM is a plain library GEMM; the tcgen05 dequant-GEMM replaces it where built."""
+    """Large-M path (prefill, batched decode): bit-exact de-quantisation of W into a bf16 scratch (the
+    reference's ``get_weight``) followed by the tcgen05/TMEM tensor-core GEMM - the reference's fallback
+    branch (quantization.py:420-421) on the 5th-generation tensor cores.  fp32 activations (tests scale
+    only) use the library GEMM."""
     w = lin.get_weight(dtype=x.dtype)
-    return torch.nn.functional.linear(x, w, lin.bias)
+    if x.dtype != torch.bfloat16 or lin.in_features % 8 != 0:
+        return torch.nn.functional.linear(x, w, lin.bias)
+    y = torch.empty((x.shape[0], lin.out_features), device=x.device, dtype=x.dtype)
+    N.call("ll_gemm_bf16_tc", N.ptr(x), N.ptr(w), N.ptr(lin.bias), N.ptr(y), x.shape[0], lin.out_features,
+           lin.in_features, N.stream())
+    return y
 
 
 def qlinear_4bit_weight(inp, weight, scales, zeros):

@@ -233,3 +233,41 @@ def test_errors_are_loud():
         ColBlockQuantizedLinear(64, 32, None, bits=4, tile_cols=-1)
     with pytest.raises(AssertionError):
         ColBlockQuantizedLinear(64, 32, False, bits=3, tile_cols=-1)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (17, 384, 512), (512, 4096, 4096), (300, 1000, 328), (640, 11008, 4096),
+                                   (4096, 12288, 1024), (130, 257, 72)])
+def test_tcgen05_gemm_vs_fp32_reference(M, N, K):
+    """tcgen05/TMEM GEMM == fp32 matmul of the same bf16 operands, up to fp32 summation order and one bf16 rounding."""
+    from lit_llama import _native as NV
+
+    g = torch.Generator(device=DEV).manual_seed(M + N + K)
+    x = torch.randn((M, K), device=DEV, generator=g).bfloat16()
+    w = (torch.randn((N, K), device=DEV, generator=g) * 0.05).bfloat16()
+    b = torch.randn((N,), device=DEV, generator=g).bfloat16()
+    for bias in (None, b):
+        y = torch.empty((M, N), device=DEV, dtype=torch.bfloat16)
+        NV.call("ll_gemm_bf16_tc", NV.ptr(x), NV.ptr(w), NV.ptr(bias), NV.ptr(y), M, N, K, NV.stream())
+        ref = x.float() @ w.float().t()
+        if bias is not None:
+            ref = ref + bias.float()
+        mag = x.float().abs() @ w.float().abs().t() + 1.0
+        err = (y.float() - ref).abs()
+        assert bool((err <= ref.abs() * 2.0**-8 + mag * 2.0**-16).all()), float((err / (ref.abs() * 2.0**-8 + mag * 2.0**-16)).max())
+
+
+@pytest.mark.parametrize("N,K,tile,M", [(4096, 4096, 128, 512), (1024, 11008, 128, 40), (384, 512, -1, 100), (512, 256, 64, 33)])
+def test_int4_large_m_linear_vs_oracle(N, K, tile, M):
+    """Prefill path: bit-exact bf16 de-quantisation + tcgen05 GEMM == the reference's fallback branch
+    F.linear(x, get_weight(bf16)) with fp32 accumulation."""
+    packed, s, z = _bf16_layer(N, K, tile, N + K + M)
+    lin = make_lin(N, K, 4, tile, s, z, "bf16", packed)
+    w = lin.get_weight(dtype=torch.bfloat16).float().cpu().numpy()
+    assert np.array_equal(w, OQ.get_weight(packed, s, z, 4, tile, "bf16"))   # fast unpack kernel: bit-exact
+    x = OQ.bf16_round(np.random.RandomState(1).randn(M, K).astype(np.float32))
+    y = lin(torch.from_numpy(x).to(DEV, torch.bfloat16)).float().cpu().numpy()
+    ref = OQ.linear_forward(x, packed, s, z, None, 4, tile, "bf16")
+    # same bf16 weights, fp32 accumulation in a different order, one bf16 rounding: 1 ulp (+ summation noise)
+    mag = np.abs(x).astype(np.float64) @ np.abs(OQ.get_weight(packed, s, z, 4, tile, "bf16")).astype(np.float64).T
+    assert (np.abs(y - ref) <= np.abs(ref) * 2.0**-7 + mag * 2.0**-16).all()
+    assert (y != ref).mean() <= 0.05
