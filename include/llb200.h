@@ -143,6 +143,22 @@ LL_API int ll_int4_gemv(const ll_gemv_args* args /* host */, ll_stream stream);
 LL_API int ll_gemm_bf16_tc(const void* x, const void* w, const void* bias, void* y, int M, int N, int K, ll_stream stream);
 
 /* ---------------------------------------------------------------------------------------
+ * llm.int8 (ref: Linear8bitLt, quantization.py:36-75; arithmetic = bitsandbytes double_quant / MatMul8bitLt,
+ * un-vendored in the reference, restated from arXiv:2208.07339 - see oracle/quant.py).
+ * ------------------------------------------------------------------------------------- */
+
+/* ref: Linear8bitLt._quantize_weight, quantization.py:67-75: W.half(), SCB[n] = absmax of row n,
+ * CB = rint(127 * W / SCB) int8 [N][K] row-major. */
+LL_API int ll_int8_quantize_weight(const void* w /*[N][K]*/, int w_dtype, int8_t* cb, float* scb, int N, int K, ll_stream stream);
+
+/* ref: bnb MatMul8bitLt forward (has_fp16_weights=False, threshold) as reached through quantization.py:36-45:
+ * y[M][N] = int8 matmul of the row-quantised non-outlier part + fp16 outlier-column part (+ bias), in the
+ * activation dtype.  K % 128 == 0.  workspace: ll_int8_workspace_bytes(min(M, 64), N, K) bytes, 256-byte aligned. */
+LL_API size_t ll_int8_workspace_bytes(int M, int N, int K);
+LL_API int ll_int8_linear(const void* x, int act_dtype, const int8_t* cb, const float* scb, const void* bias, void* y, int M,
+                   int N, int K, float threshold, void* workspace, size_t workspace_bytes, ll_stream stream);
+
+/* ---------------------------------------------------------------------------------------
  * model.py kernels
  * ------------------------------------------------------------------------------------- */
 

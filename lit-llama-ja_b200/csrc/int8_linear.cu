@@ -1,0 +1,298 @@
+// llm.int8 (LLM.int8(), arXiv:2208.07339) Linear for sm_100a: row-wise int8 weight quantisation and the
+// outlier-decomposed int8 x int8 -> int32 matmul.
+// ref: /root/reference/lit_llama/quantization.py:36-75 (Linear8bitLt over bitsandbytes, has_fp16_weights=False,
+// threshold=6.0).  bitsandbytes itself is un-vendored and unpinned in the reference, so the arithmetic follows
+// the published algorithm as restated in oracle/quant.py (int8_quantize_weight, int8_linear_forward):
+//   A = x.half(); outlier columns = features with any |A| >= threshold;
+//   SCA[m] = absmax over the entries of row m below the threshold; CA = rint(127 A / SCA), outlier columns 0;
+//   C32 = CA . CB^T (int32, exact); out = fp16(C32 * SCA * SCB / 127^2 (+ bias));
+//   out = fp16(out + fp16(A[:, idx] . fp16(CB[:, idx] * SCB / 127)^T)); cast to the input dtype.
+// Decode-shaped (M <= 64 per pass): HBM-bound on the int8 weight read (N*K bytes per layer).  The integer
+// part runs on the tensor cores (mma.sync m16n8k32 s8) with the weights as the A operand straight from
+// global memory in 16-byte loads; K is split across CTAs and combined with int32 atomics (integer addition
+// is associative: bit-deterministic).
+#include "common.cuh"
+
+namespace llb {
+namespace {
+
+template <typename T> __device__ __forceinline__ float to_half_f32(T v);
+template <> __device__ __forceinline__ float to_half_f32<float>(float v) { return __half2float(__float2half_rn(v)); }
+template <> __device__ __forceinline__ float to_half_f32<__nv_bfloat16>(__nv_bfloat16 v) {
+  return __half2float(__float2half_rn(__bfloat162float(v)));
+}
+template <> __device__ __forceinline__ float to_half_f32<__half>(__half v) { return __half2float(v); }
+
+// ---------------------------------------------------------------- weight quantisation (load time)
+template <typename T>
+__global__ void int8_quant_weight_kernel(const T* __restrict__ w, int8_t* __restrict__ cb, float* __restrict__ scb, int K) {
+  __shared__ float red[32];
+  const T* row = w + (size_t)blockIdx.x * K;
+  float mx = 0.f;
+  for (int k = threadIdx.x; k < K; k += blockDim.x) mx = fmaxf(mx, fabsf(to_half_f32<T>(row[k])));
+  mx = warp_max(mx);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+    v = warp_max(v);
+    if (threadIdx.x == 0) red[0] = v;
+  }
+  __syncthreads();
+  mx = red[0];
+  if (threadIdx.x == 0) scb[blockIdx.x] = mx;
+  const float inv = __fdiv_rn(127.f, mx == 0.f ? 1.f : mx);
+  for (int k = threadIdx.x; k < K; k += blockDim.x) {
+    const float q = rintf(__fmul_rn(to_half_f32<T>(row[k]), inv));
+    cb[(size_t)blockIdx.x * K + k] = (int8_t)fminf(fmaxf(q, -127.f), 127.f);
+  }
+}
+
+// ---------------------------------------------------------------- activation statistics
+// a16 = x.half(); colflag[k] = any |a16[:,k]| >= thr; sca_bits[m] = max over entries below thr (float bits, >= 0)
+template <typename T>
+__global__ void int8_act_stats_kernel(const T* __restrict__ x, __half* __restrict__ a16, int32_t* __restrict__ colflag,
+                                      int32_t* __restrict__ sca_bits, int M, int K, float thr) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int m0 = blockIdx.y * 8;
+  bool flag = false;
+  for (int m = m0; m < min(m0 + 8, M); ++m) {
+    float v = 0.f;
+    if (k < K) {
+      const __half h = __float2half_rn(to_half_f32<T>(x[(size_t)m * K + k]));
+      a16[(size_t)m * K + k] = h;
+      v = fabsf(__half2float(h));
+    }
+    const bool big = v >= thr;
+    flag |= big;
+    float mx = big ? 0.f : v;
+    mx = warp_max(mx);
+    if ((threadIdx.x & 31) == 0 && mx > 0.f) atomicMax(&sca_bits[m], __float_as_int(mx));
+  }
+  if (flag && k < K) colflag[k] = 1;
+}
+
+// ascending list of outlier columns (single block; deterministic order)
+__global__ void int8_compact_cols_kernel(const int32_t* __restrict__ colflag, int32_t* __restrict__ idx, int32_t* __restrict__ count,
+                                         int K) {
+  __shared__ int s_base;
+  __shared__ int s_warp[32];
+  if (threadIdx.x == 0) s_base = 0;
+  __syncthreads();
+  for (int k0 = 0; k0 < K; k0 += blockDim.x) {
+    const int k = k0 + threadIdx.x;
+    const int f = (k < K && colflag[k] != 0) ? 1 : 0;
+    const unsigned bal = __ballot_sync(0xffffffffu, f);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) s_warp[warp] = __popc(bal);
+    __syncthreads();
+    int off = s_base;
+    for (int w = 0; w < warp; ++w) off += s_warp[w];
+    if (f) idx[off + __popc(bal & ((1u << lane) - 1u))] = k;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int t = 0;
+      for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += s_warp[w];
+      s_base += t;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *count = s_base;
+}
+
+// CA[m][k] = colflag[k] ? 0 : clip(rint(a16 * 127 / SCA[m]), -127, 127), entries >= thr are 0 as well
+__global__ void int8_act_quant_kernel(const __half* __restrict__ a16, const int32_t* __restrict__ colflag,
+                                      const int32_t* __restrict__ sca_bits, int8_t* __restrict__ ca, int M, int K, float thr) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int m = blockIdx.y;
+  if (k >= K) return;
+  const float sca = __int_as_float(sca_bits[m]);
+  const float inv = __fdiv_rn(127.f, sca == 0.f ? 1.f : sca);
+  const float a = __half2float(a16[(size_t)m * K + k]);
+  float q = 0.f;
+  if (colflag[k] == 0 && fabsf(a) < thr) q = fminf(fmaxf(rintf(__fmul_rn(a, inv)), -127.f), 127.f);
+  ca[(size_t)m * K + k] = (int8_t)q;
+}
+
+// ---------------------------------------------------------------- int8 tensor-core matmul, split-K
+__device__ __forceinline__ void mma_s8_16832(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                             uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// grid (N/16 tiles, ksplit); block = 4 warps, each takes every 4th 128-k block of the CTA's k range.
+// c32[m][n] += sum_k CA[m][k] * CB[n][k]   (M <= 8 * MG rows; weights are the MMA A operand)
+template <int MG>
+__global__ void __launch_bounds__(128) int8_mm_kernel(const int8_t* __restrict__ cb, const int8_t* __restrict__ ca,
+                                                      int32_t* __restrict__ c32, int M, int N, int K, int kblocks_per_split) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tig = lane & 3;
+  const int n0 = blockIdx.x * 16;
+  const int nkb = K / 128;
+  const int kb0 = blockIdx.y * kblocks_per_split, kb1 = min(kb0 + kblocks_per_split, nkb);
+  int acc[MG][4];
+#pragma unroll
+  for (int i = 0; i < MG; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0;
+  const int8_t* w_lo = cb + (size_t)(n0 + g) * K + 16 * tig;
+  const int8_t* w_hi = cb + (size_t)(n0 + g + 8) * K + 16 * tig;
+  const bool n_lo_ok = n0 + g < N, n_hi_ok = n0 + g + 8 < N;
+  for (int kb = kb0 + warp; kb < kb1; kb += 4) {
+    const int k = kb * 128;
+    // lane (g, tig) holds k = k + 16 tig + [0,16) (slots 0..15 of four MMAs) and k + 64 + 16 tig + [0,16)
+    const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+    const uint4 a_lo0 = n_lo_ok ? __ldcs(reinterpret_cast<const uint4*>(w_lo + k)) : z4;
+    const uint4 a_hi0 = n_hi_ok ? __ldcs(reinterpret_cast<const uint4*>(w_hi + k)) : z4;
+    const uint4 a_lo1 = n_lo_ok ? __ldcs(reinterpret_cast<const uint4*>(w_lo + k + 64)) : z4;
+    const uint4 a_hi1 = n_hi_ok ? __ldcs(reinterpret_cast<const uint4*>(w_hi + k + 64)) : z4;
+    const uint32_t al0[4] = {a_lo0.x, a_lo0.y, a_lo0.z, a_lo0.w}, ah0[4] = {a_hi0.x, a_hi0.y, a_hi0.z, a_hi0.w};
+    const uint32_t al1[4] = {a_lo1.x, a_lo1.y, a_lo1.z, a_lo1.w}, ah1[4] = {a_hi1.x, a_hi1.y, a_hi1.z, a_hi1.w};
+#pragma unroll
+    for (int mg = 0; mg < MG; ++mg) {
+      const int m = mg * 8 + g;
+      uint4 b0 = z4, b1 = z4;
+      if (m < M) {
+        b0 = __ldg(reinterpret_cast<const uint4*>(ca + (size_t)m * K + k + 16 * tig));
+        b1 = __ldg(reinterpret_cast<const uint4*>(ca + (size_t)m * K + k + 64 + 16 * tig));
+      }
+      const uint32_t bb0[4] = {b0.x, b0.y, b0.z, b0.w}, bb1[4] = {b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) mma_s8_16832(acc[mg], al0[j], ah0[j], al1[j], ah1[j], bb0[j], bb1[j]);
+    }
+  }
+  // D: c0,c1 -> (n = n0+g, m = 2tig, 2tig+1); c2,c3 -> (n = n0+g+8, ...)
+#pragma unroll
+  for (int mg = 0; mg < MG; ++mg) {
+    const int m0 = mg * 8 + 2 * tig;
+    if (m0 < M) {
+      if (n_lo_ok && acc[mg][0] != 0) atomicAdd(&c32[(size_t)m0 * N + n0 + g], acc[mg][0]);
+      if (n_hi_ok && acc[mg][2] != 0) atomicAdd(&c32[(size_t)m0 * N + n0 + g + 8], acc[mg][2]);
+    }
+    if (m0 + 1 < M) {
+      if (n_lo_ok && acc[mg][1] != 0) atomicAdd(&c32[(size_t)(m0 + 1) * N + n0 + g], acc[mg][1]);
+      if (n_hi_ok && acc[mg][3] != 0) atomicAdd(&c32[(size_t)(m0 + 1) * N + n0 + g + 8], acc[mg][3]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- dequantise + outlier part + store
+template <typename T>
+__global__ void int8_finish_kernel(const int32_t* __restrict__ c32, const int32_t* __restrict__ sca_bits, const float* __restrict__ scb,
+                                   const T* __restrict__ bias, const __half* __restrict__ a16, const int8_t* __restrict__ cb,
+                                   const int32_t* __restrict__ idx, const int32_t* __restrict__ count, T* __restrict__ y, int M,
+                                   int N, int K) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  const int m = blockIdx.y;
+  if (n >= N) return;
+  const float sca = __int_as_float(sca_bits[m]);
+  const float sb = scb[n];
+  float out = __fmul_rn(__fmul_rn(__fmul_rn((float)c32[(size_t)m * N + n], sca), sb), 1.0f / (127.0f * 127.0f));
+  if (bias != nullptr) out = __fadd_rn(out, to_half_f32<T>(bias[n]));
+  out = __half2float(__float2half_rn(out));
+  const int cnt = *count;
+  if (cnt > 0) {
+    float acc = 0.f;
+    for (int i = 0; i < cnt; ++i) {
+      const int k = idx[i];
+      const float wv = __half2float(__float2half_rn(__fdiv_rn(__fmul_rn((float)cb[(size_t)n * K + k], sb), 127.f)));
+      acc = fmaf(__half2float(a16[(size_t)m * K + k]), wv, acc);
+    }
+    out = __half2float(__float2half_rn(__fadd_rn(out, __half2float(__float2half_rn(acc)))));
+  }
+  dt<T>::st(y, (size_t)m * N + n, out);
+}
+
+struct Ws {
+  __half* a16; int8_t* ca; int32_t* c32; int32_t* colflag; int32_t* idx; int32_t* sca_bits; int32_t* count;
+  size_t zero_off, zero_bytes, total;
+};
+Ws carve(void* base, int M, int N, int K) {
+  Ws w;
+  size_t o = 0;
+  auto take = [&](size_t b) { size_t r = o; o += (b + 255) & ~(size_t)255; return r; };
+  uint8_t* p = (uint8_t*)base;
+  w.a16 = (__half*)(p + take((size_t)M * K * 2));
+  w.ca = (int8_t*)(p + take((size_t)M * K));
+  w.idx = (int32_t*)(p + take((size_t)K * 4));
+  w.zero_off = o;  // everything below is cleared at the start of every call
+  w.c32 = (int32_t*)(p + take((size_t)M * N * 4));
+  w.colflag = (int32_t*)(p + take((size_t)K * 4));
+  w.sca_bits = (int32_t*)(p + take((size_t)M * 4));
+  w.count = (int32_t*)(p + take(4));
+  w.zero_bytes = o - w.zero_off;
+  w.total = o;
+  return w;
+}
+
+}  // namespace
+}  // namespace llb
+
+using namespace llb;
+
+template <typename T>
+static int int8_linear_t(const T* x, const int8_t* cb, const float* scb, const T* bias, T* y, int M, int N, int K, float thr,
+                         void* ws_base, cudaStream_t st) {
+  const int sms = sm_count();
+  for (int m0 = 0; m0 < M; m0 += 64) {  // decode-shaped passes of up to 64 rows (weights re-read per pass)
+    const int Mp = min(64, M - m0);
+    Ws w = carve(ws_base, Mp, N, K);
+    LL_CUDA(cudaMemsetAsync((uint8_t*)ws_base + w.zero_off, 0, w.zero_bytes, st));
+    const T* xp = x + (size_t)m0 * K;
+    int8_act_stats_kernel<T><<<dim3((K + 255) / 256, (Mp + 7) / 8), 256, 0, st>>>(xp, w.a16, w.colflag, w.sca_bits, Mp, K, thr);
+    int8_compact_cols_kernel<<<1, 1024, 0, st>>>(w.colflag, w.idx, w.count, K);
+    int8_act_quant_kernel<<<dim3((K + 255) / 256, Mp), 256, 0, st>>>(w.a16, w.colflag, w.sca_bits, w.ca, Mp, K, thr);
+    const int ntiles = (N + 15) / 16, nkb = K / 128;
+    int ksplit = (2 * sms + ntiles - 1) / ntiles;
+    if (ksplit > nkb) ksplit = nkb;
+    if (ksplit < 1) ksplit = 1;
+    const int per = (nkb + ksplit - 1) / ksplit;
+    ksplit = (nkb + per - 1) / per;
+    dim3 grid(ntiles, ksplit);
+    const int mg = (Mp + 7) / 8;
+#define MM(G) int8_mm_kernel<G><<<grid, 128, 0, st>>>(cb, w.ca, w.c32, Mp, N, K, per)
+    if (mg <= 1) MM(1); else if (mg <= 2) MM(2); else if (mg <= 4) MM(4); else MM(8);
+#undef MM
+    int8_finish_kernel<T><<<dim3((N + 127) / 128, Mp), 128, 0, st>>>(w.c32, w.sca_bits, scb, bias, w.a16, cb, w.idx, w.count,
+                                                                    y + (size_t)m0 * N, Mp, N, K);
+    LL_LAUNCH_OK("int8 linear kernels");
+  }
+  return LL_OK;
+}
+
+extern "C" {
+
+size_t ll_int8_workspace_bytes(int M, int N, int K) { return carve(nullptr, M, N, K).total; }
+
+int ll_int8_quantize_weight(const void* w, int w_dtype, int8_t* cb, float* scb, int N, int K, ll_stream stream) {
+  LL_CHECK_ARG(w && cb && scb && N > 0 && K > 0, "bad int8_quantize_weight arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (w_dtype == LL_F32) int8_quant_weight_kernel<float><<<N, 256, 0, st>>>((const float*)w, cb, scb, K);
+  else if (w_dtype == LL_BF16) int8_quant_weight_kernel<__nv_bfloat16><<<N, 256, 0, st>>>((const __nv_bfloat16*)w, cb, scb, K);
+  else if (w_dtype == LL_F16) int8_quant_weight_kernel<__half><<<N, 256, 0, st>>>((const __half*)w, cb, scb, K);
+  else {
+    set_error("int8_quantize_weight: unsupported dtype %d", w_dtype);
+    return LL_ERR_UNSUPPORTED;
+  }
+  LL_LAUNCH_OK("int8_quant_weight_kernel");
+  return LL_OK;
+}
+
+int ll_int8_linear(const void* x, int act_dtype, const int8_t* cb, const float* scb, const void* bias, void* y, int M, int N,
+                   int K, float threshold, void* workspace, size_t workspace_bytes, ll_stream stream) {
+  LL_CHECK_ARG(x && cb && scb && y && workspace, "null pointer");
+  LL_CHECK_ARG(M > 0 && N > 0 && K > 0 && K % 128 == 0, "int8 linear needs K %% 128 == 0 (M=%d N=%d K=%d)", M, N, K);
+  LL_CHECK_ARG(((uintptr_t)cb & 15) == 0 && ((uintptr_t)workspace & 255) == 0, "cb must be 16-byte, workspace 256-byte aligned");
+  LL_CHECK_ARG(workspace_bytes >= ll_int8_workspace_bytes(M < 64 ? M : 64, N, K), "workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (act_dtype == LL_BF16)
+    return int8_linear_t<__nv_bfloat16>((const __nv_bfloat16*)x, cb, scb, (const __nv_bfloat16*)bias, (__nv_bfloat16*)y, M, N, K, threshold, workspace, st);
+  if (act_dtype == LL_F16)
+    return int8_linear_t<__half>((const __half*)x, cb, scb, (const __half*)bias, (__half*)y, M, N, K, threshold, workspace, st);
+  if (act_dtype == LL_F32)
+    return int8_linear_t<float>((const float*)x, cb, scb, (const float*)bias, (float*)y, M, N, K, threshold, workspace, st);
+  set_error("int8_linear: unsupported activation dtype %d", act_dtype);
+  return LL_ERR_UNSUPPORTED;
+}
+
+}  // extern "C"

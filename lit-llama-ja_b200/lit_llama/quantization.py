@@ -203,12 +203,90 @@ def qlinear_4bit_weight(inp, weight, scales, zeros):
     return lin(inp)
 
 
-class Linear8bitLt(torch.nn.Linear):
-    """LLM.int8() Linear (ref: quantization.py:36-75, wrapping bitsandbytes).  Placeholder until the
-    sm_100a int8 kernels land: constructing it fails loudly rather than falling back."""
+class Linear8bitLt(torch.nn.Module):
+    """LLM.int8() Linear (ref: quantization.py:36-75, which wraps ``bnb.nn.Linear8bitLt`` with
+    ``has_fp16_weights=False, threshold=6.0``).  Same surface: called like ``nn.Linear(in, out, bias=True)``;
+    ``weight`` is an int8 Parameter (row-major ``CB``) carrying the attributes ``CB`` and ``SCB`` (row absmax);
+    loading a state dict takes the floating-point ``weight`` of an ordinary checkpoint and re-quantizes it
+    (there is no int8 checkpoint format).  CUDA only.
 
-    def __init__(self, *args, **kwargs):
-        raise NotImplementedError("llm.int8 kernels are not built yet in this revision")
+    One deviation, on purpose: the reference's ``_load_from_state_dict`` picks the first key of the WHOLE
+    state dict that ends in ``weight`` (quantization.py:52-55), which is only right for the first module
+    loaded; this one looks up ``prefix + "weight"``."""
+
+    threshold = 6.0
+
+    def __init__(self, in_features, out_features, bias=True, device=None, dtype=None, **kwargs):
+        super().__init__()
+        self.in_features, self.out_features = in_features, out_features
+        dev = torch.device(device) if device is not None else torch.empty(0).device
+        if dev.type != "cuda":
+            raise RuntimeError("Linear8bitLt (llm.int8) needs a CUDA device: there is no CPU fallback")
+        self.weight = torch.nn.Parameter(torch.zeros((out_features, in_features), dtype=torch.int8, device=dev),
+                                         requires_grad=False)
+        self.weight.CB = self.weight.data
+        self.weight.SCB = torch.zeros(out_features, dtype=torch.float32, device=dev)
+        self.bias = torch.nn.Parameter(torch.zeros(out_features, device=dev, dtype=dtype), requires_grad=False) if bias else None
+        self._ws = None
+
+    def _load_from_state_dict(self, state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys, error_msgs):
+        key = prefix + "weight"
+        if key in state_dict:
+            w = state_dict[key]
+            if w.dtype == torch.int8:      # a state dict saved from this module: CB as is, SCB cannot be recovered
+                raise RuntimeError("Linear8bitLt loads the floating-point weight of an ordinary checkpoint (ref quantization.py:50-65)")
+            self._quantize_weight(w)
+        elif strict:
+            missing_keys.append(key)
+        bkey = prefix + "bias"
+        if self.bias is not None:
+            if bkey in state_dict:
+                self.bias.data.copy_(state_dict[bkey])
+            elif strict:
+                missing_keys.append(bkey)
+        elif bkey in state_dict and strict:
+            unexpected_keys.append(bkey)
+
+    def _quantize_weight(self, weight: torch.Tensor) -> None:
+        """ref: quantization.py:67-75 - ``weight.half()``, row absmax ``SCB``, ``CB = rint(127 W / SCB)``."""
+        dev = self.weight.device
+        w = weight.to(device=dev).contiguous()
+        if w.dtype not in (torch.float32, torch.bfloat16, torch.float16):
+            w = w.float()
+        assert w.shape == (self.out_features, self.in_features)
+        cb = torch.empty(w.shape, dtype=torch.int8, device=dev)
+        scb = torch.empty(w.shape[0], dtype=torch.float32, device=dev)
+        N.call("ll_int8_quantize_weight", N.ptr(w), N.dtype_code(w.dtype), N.ptr(cb), N.ptr(scb), w.shape[0], w.shape[1], N.stream())
+        self.weight.data = cb
+        self.weight.CB, self.weight.SCB = cb, scb
+
+    def forward(self, inp):
+        N.require_cuda(inp, self.weight)
+        K, Nout = self.in_features, self.out_features
+        assert inp.shape[-1] == K, "incompatible dimensions"
+        x = inp.reshape(-1, K).contiguous()
+        M = x.shape[0]
+        if M == 0:
+            return inp.new_empty(inp.shape[:-1] + (Nout,))
+        y = torch.empty((M, Nout), device=x.device, dtype=x.dtype)
+        need = N._fn["ll_int8_workspace_bytes"](min(M, 64), Nout, K)
+        ws = _int8_workspace(x.device, need)
+        bias = None if self.bias is None else self.bias.to(x.dtype)
+        N.call("ll_int8_linear", N.ptr(x), N.dtype_code(x.dtype), N.ptr(self.weight.CB), N.ptr(self.weight.SCB), N.ptr(bias),
+               N.ptr(y), M, Nout, K, float(self.threshold), N.ptr(ws), ws.numel(), N.stream())
+        return y.reshape(inp.shape[:-1] + (Nout,))
+
+
+_INT8_WS: dict = {}
+
+
+def _int8_workspace(device, nbytes: int) -> torch.Tensor:
+    """Per-(device, stream) scratch of the int8 linear (kernels on one stream are ordered)."""
+    key = (device.index, torch.cuda.current_stream().cuda_stream)
+    ws = _INT8_WS.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = _INT8_WS[key] = torch.empty(nbytes + 256, dtype=torch.uint8, device=device)
+    return ws
 
 
 # --------------------------------------------------------------------------------------- row Z
