@@ -21,8 +21,16 @@ import os
 
 import torch
 
+import torch.distributed as dist
+
 from . import _native as N
 from .quantization import ColBlockQuantizedLinear
+
+
+def _unwrap(lin):
+    """(quantized Linear, process group or None) - row-parallel shards come wrapped (tensor_parallel.py)."""
+    inner = getattr(lin, "inner", None)
+    return (inner, getattr(lin, "group", None)) if inner is not None else (lin, None)
 
 
 def _env_flag(name: str, default: bool) -> bool:
@@ -43,7 +51,7 @@ class DecodeEngine:
             return False
         lins = [model.lm_head]
         for blk in model.transformer.h:
-            lins += [blk.attn.c_attn, blk.attn.c_proj, blk.mlp.c_fc1, blk.mlp.c_fc2, blk.mlp.c_proj]
+            lins += [blk.attn.c_attn, _unwrap(blk.attn.c_proj)[0], blk.mlp.c_fc1, blk.mlp.c_fc2, _unwrap(blk.mlp.c_proj)[0]]
             if blk.rms_1.scale.dtype != torch.bfloat16:
                 return False
         for lin in lins:
@@ -54,23 +62,28 @@ class DecodeEngine:
         for blk in model.transformer.h:
             if blk.mlp.c_fc1.tile_cols != blk.mlp.c_fc2.tile_cols:
                 return False
-        E, H, V = cfg.n_embd, cfg.n_hidden, cfg.padded_vocab_size
         h0 = model.transformer.h[0]
-        shapes = [(3 * E, E, h0.attn.c_attn.tile_cols, 1), (E, E, h0.attn.c_proj.tile_cols, 1),
-                  (H, E, h0.mlp.c_fc1.tile_cols, 2), (E, H, h0.mlp.c_proj.tile_cols, 1), (V, E, model.lm_head.tile_cols, 1)]
-        return all(N.gemv_supported(n, k, g, nmat, B) for n, k, g, nmat in shapes)
+        shapes = [(h0.attn.c_attn, 1), (_unwrap(h0.attn.c_proj)[0], 1), (h0.mlp.c_fc1, 2), (_unwrap(h0.mlp.c_proj)[0], 1),
+                  (model.lm_head, 1)]
+        return all(N.gemv_supported(l.out_features, l.in_features, l.tile_cols, nmat, B) for l, nmat in shapes)
 
     def __init__(self, model, B: int, max_seq_length: int):
         cfg = model.config
         self.model, self.B, self.S = model, B, max_seq_length
         dev = model.transformer.wte.weight.device
-        E, H, V = cfg.n_embd, cfg.n_hidden, cfg.padded_vocab_size
+        h0 = model.transformer.h[0]
+        self.tp_group = _unwrap(h0.attn.c_proj)[1] if getattr(model, "_tp", None) is not None else None
+        self.tp = getattr(model, "_tp", None) is not None
+        self.nh = h0.attn.n_head                      # heads on this rank
+        E, V = cfg.n_embd, cfg.padded_vocab_size
+        E_loc, H = self.nh * cfg.head_size, h0.mlp.c_fc1.out_features
         bf, f32, i32 = torch.bfloat16, torch.float32, torch.int32
         self.tok = torch.zeros(B, dtype=torch.int64, device=dev)
         self.pos = torch.zeros(3, dtype=i32, device=dev)
         self.x = torch.zeros((B, E), dtype=bf, device=dev)        # residual stream
-        self.q = torch.zeros((B, E), dtype=bf, device=dev)
-        self.att = torch.zeros((B, E), dtype=bf, device=dev)
+        self.q = torch.zeros((B, E_loc), dtype=bf, device=dev)
+        self.att = torch.zeros((B, E_loc), dtype=bf, device=dev)
+        self.part = torch.zeros((B, E), dtype=bf, device=dev)     # row-parallel partial result (tensor parallel only)
         self.h = torch.zeros((B, H), dtype=bf, device=dev)
         self.logits = torch.zeros((B, V), dtype=bf, device=dev)
         self.rope = model._rope_f32
@@ -82,7 +95,7 @@ class DecodeEngine:
         self.n_launches = 0
         self.n_replays = 0
 
-        nh, hs = cfg.n_head, cfg.head_size
+        nh, hs = self.nh, cfg.head_size
         self.splits = max(1, min(16, (2 * N._fn["ll_sm_count"]()) // max(1, B * nh), (max_seq_length + 63) // 64))
         self.attn_scratch = torch.empty(N.attn_scratch_bytes(B, nh, hs, self.splits) // 4 + 16, dtype=f32, device=dev)
         self.attn_counters = torch.zeros(B * nh, dtype=i32, device=dev)
@@ -125,10 +138,12 @@ class DecodeEngine:
             a_attn = self._gemv_args(blk.attn.c_attn, self.x, self.q, N.EPI_ROPE_KV, "attn", norm=blk.rms_1)
             a_attn.rope, a_attn.pos = self.rope.data_ptr(), self.pos.data_ptr()
             a_attn.k_cache, a_attn.v_cache = kc.data_ptr(), vc.data_ptr()
-            a_attn.n_head, a_attn.head_size, a_attn.cache_len = cfg.n_head, cfg.head_size, self.S
-            a_proj = self._gemv_args(blk.attn.c_proj, self.att, self.x, N.EPI_RESIDUAL, "proj")
+            a_attn.n_head, a_attn.head_size, a_attn.cache_len = self.nh, cfg.head_size, self.S
+            # tensor parallel: the row-parallel GEMVs store their partial sums; all-reduce, then the residual add
+            out, epi = (self.part, N.EPI_STORE) if self.tp else (self.x, N.EPI_RESIDUAL)
+            a_proj = self._gemv_args(_unwrap(blk.attn.c_proj)[0], self.att, out, epi, "proj")
             a_fc = self._gemv_args(blk.mlp.c_fc1, self.x, self.h, N.EPI_SWIGLU, "fc", norm=blk.rms_2, lin2=blk.mlp.c_fc2)
-            a_down = self._gemv_args(blk.mlp.c_proj, self.h, self.x, N.EPI_RESIDUAL, "down")
+            a_down = self._gemv_args(_unwrap(blk.mlp.c_proj)[0], self.h, out, epi, "down")
             self.layers.append((a_attn, kc, vc, a_proj, a_fc, a_down))
         self.a_head = self._gemv_args(m.lm_head, self.x, self.logits, N.EPI_STORE, "head", norm=m.transformer.ln_f)
 
@@ -143,14 +158,23 @@ class DecodeEngine:
         for a_attn, kc, vc, a_proj, a_fc, a_down in self.layers:
             N.gemv(a_attn)
             N.call("ll_decode_attn", N.ptr(self.q), N.ptr(kc), N.ptr(vc), N.ptr(self.pos), N.ptr(self.att), N.LL_BF16,
-                   self.B, cfg.n_head, cfg.head_size, self.S, self.splits, N.ptr(self.attn_scratch),
+                   self.B, self.nh, cfg.head_size, self.S, self.splits, N.ptr(self.attn_scratch),
                    N.ptr(self.attn_counters), flags, st)
             N.gemv(a_proj)
+            if self.tp:
+                self._reduce_add()
             N.gemv(a_fc)
             N.gemv(a_down)
-            n += 5
+            if self.tp:
+                self._reduce_add()
+            n += 5 + (2 if self.tp else 0)
         N.gemv(self.a_head)
         self.n_launches = n + 1
+
+    def _reduce_add(self):
+        """x += all_reduce(partial): the path's only exchange step (NCCL over NVLink; captured in the graph)."""
+        dist.all_reduce(self.part, op=dist.ReduceOp.SUM, group=self.tp_group)
+        N.call("ll_add", N.ptr(self.x), N.ptr(self.part), N.ptr(self.x), N.LL_BF16, self.x.numel(), N.stream())
 
     def _capture(self):
         # warm up eagerly on a side stream (also sizes kernel attributes), then capture

@@ -126,13 +126,15 @@ class CausalSelfAttention(nn.Module):
         assert config.n_embd % config.n_head == 0
         self.c_attn = nn.Linear(config.n_embd, 3 * config.n_embd, bias=False)
         self.c_proj = nn.Linear(config.n_embd, config.n_embd, bias=False)
-        self.n_head = config.n_head
+        self.n_head = config.n_head          # heads held by THIS rank (tensor_parallel.py lowers it)
+        self.head_size = config.n_embd // config.n_head
         self.n_embd = config.n_embd
         self.block_size = config.block_size
 
     def forward(self, x: torch.Tensor, step: _Step, kv_cache: Optional[KVCache] = None):
-        B, T, C = x.shape
-        nh, hs = self.n_head, C // self.n_head
+        B, T, _ = x.shape
+        nh, hs = self.n_head, self.head_size
+        C = nh * hs                                             # width of this rank's attention output
         qkv = self.c_attn(x).contiguous()                       # [B, T, 3C], rows ordered [q; k; v]
         if kv_cache is None:                                    # no-cache forward: a T-slot scratch cache
             S = T
@@ -294,7 +296,7 @@ class LLaMA(nn.Module):
                 x, _ = block(x, step)
         else:
             if not self.kv_caches:
-                shape = (B, self.config.n_head, max_seq_length, self.config.head_size)
+                shape = (B, self.transformer.h[0].attn.n_head, max_seq_length, self.config.head_size)
                 self.kv_caches = [(torch.zeros(shape, device=dev, dtype=x.dtype), torch.zeros(shape, device=dev, dtype=x.dtype))
                                   for _ in range(self.config.n_layer)]
             for i, block in enumerate(self.transformer.h):
@@ -313,7 +315,7 @@ class LLaMA(nn.Module):
         if not DecodeEngine.eligible(self, B):
             return None
         if not self.kv_caches:
-            shape = (B, self.config.n_head, max_seq_length, self.config.head_size)
+            shape = (B, self.transformer.h[0].attn.n_head, max_seq_length, self.config.head_size)
             dev = self.transformer.wte.weight.device
             self.kv_caches = [(torch.zeros(shape, device=dev, dtype=torch.bfloat16),
                                torch.zeros(shape, device=dev, dtype=torch.bfloat16)) for _ in range(self.config.n_layer)]
