@@ -159,6 +159,16 @@ LL_API int ll_int8_linear(const void* x, int act_dtype, const int8_t* cb, const 
                    int N, int K, float threshold, void* workspace, size_t workspace_bytes, ll_stream stream);
 
 /* ---------------------------------------------------------------------------------------
+ * Tensor-parallel exchange (new: the reference is single-device, generate.py:122).  One-shot all-reduce over
+ * NVLink peer memory fused with the residual add: x = bf16(x + bf16(sum over ranks of part_r)), summed in rank
+ * order on every rank.  peer_parts / peer_flags: HOST arrays of `world` device pointers (symmetric-memory mappings
+ * of every rank's partial-sum buffer and int32[world] flag array, zeroed once).  The caller alternates between two
+ * partial-sum buffers from call to call.  epoch_counter: local device int32, zero before first use.
+ * ------------------------------------------------------------------------------------- */
+LL_API int ll_tp_allreduce_add(void* x, const uint64_t* peer_parts, const uint64_t* peer_flags, int32_t* epoch_counter, int rank,
+                        int world, int n, ll_stream stream);
+
+/* ---------------------------------------------------------------------------------------
  * model.py kernels
  * ------------------------------------------------------------------------------------- */
 

@@ -1,0 +1,106 @@
+// One-shot all-reduce over NVLink peer memory for the tensor-parallel decode step, fused with the residual add:
+//   x[i] = bf16( x[i] + bf16( sum_r part_r[i] ) )        (r in rank order on every rank: identical bits everywhere)
+// ref: none - the reference is single-device (generate.py:122); this is the one exchange step of the sharded path
+// (SURVEY 8e): [B, n_embd] bf16 after each row-parallel GEMV (16 KB at batch 1 for 65B), latency-bound.  NCCL's
+// all-reduce costs a launch + protocol round per call and does not sit well inside a captured graph next to PDL
+// kernels; here every rank pushes nothing - it only raises a flag, then PULLS the peers' partial sums straight out of
+// their HBM through the NVSwitch (P2P loads on symmetric-memory mappings), so one small kernel is the whole
+// collective.  Double-buffered partials (the caller alternates buffers) make one flag exchange per call enough:
+// a peer can only overwrite buffer b two calls later, after it has seen this rank's next flag, which this rank
+// raises only when it has finished reading.
+#include "common.cuh"
+
+namespace llb {
+namespace {
+
+constexpr int MAX_WORLD = 16;
+
+struct TpArgs {
+  const __nv_bfloat16* part[MAX_WORLD];  // peer-mapped partial-sum buffers (entry `rank` is the local one)
+  int32_t* flags[MAX_WORLD];             // peer-mapped flag arrays: flags[r][s] = last epoch rank s announced to rank r
+};
+
+__device__ __forceinline__ void st_release_sys(int32_t* p, int32_t v) {
+  asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
+  int32_t v;
+  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ld_relaxed_sys_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(1024) tp_allreduce_add_kernel(const __grid_constant__ TpArgs a, __nv_bfloat16* __restrict__ x,
+                                                                int32_t* __restrict__ epoch_counter, int rank, int world, int n) {
+  __shared__ int s_epoch;
+  if (threadIdx.x == 0) s_epoch = ++(*epoch_counter);  // same call count on every rank -> same epoch
+  __syncthreads();
+  const int epoch = s_epoch;
+  // announce: "my partial sums of this epoch are in my buffer" (written by the previous kernel of this stream)
+  if (threadIdx.x < world) st_release_sys(a.flags[threadIdx.x] + rank, epoch);
+  // wait for every rank's announcement
+  if (threadIdx.x < world) {
+    const int32_t* f = a.flags[rank] + threadIdx.x;
+    while (ld_acquire_sys(f) < epoch) {
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x * 8; i < n; i += blockDim.x * 8) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int r = 0; r < world; ++r) {
+      const uint4 v = ld_relaxed_sys_v4(a.part[r] + i);
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        acc[2 * e] += bf16_bits_to_f32(w[e] & 0xffffu);
+        acc[2 * e + 1] += bf16_bits_to_f32(w[e] >> 16);
+      }
+    }
+    const uint4 xv = *reinterpret_cast<const uint4*>(x + i);
+    const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float h0 = bf16r(acc[2 * e]), h1 = bf16r(acc[2 * e + 1]);
+      const uint32_t lo = f32_to_bf16_bits(__fadd_rn(bf16_bits_to_f32(xw[e] & 0xffffu), h0));
+      const uint32_t hi = f32_to_bf16_bits(__fadd_rn(bf16_bits_to_f32(xw[e] >> 16), h1));
+      o[e] = lo | (hi << 16);
+    }
+    *reinterpret_cast<uint4*>(x + i) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+}  // namespace
+}  // namespace llb
+
+using namespace llb;
+
+extern "C" {
+
+int ll_tp_allreduce_add(void* x, const uint64_t* peer_parts /* host: world pointers */, const uint64_t* peer_flags /* host */,
+                        int32_t* epoch_counter, int rank, int world, int n, ll_stream stream) {
+  LL_CHECK_ARG(x && peer_parts && peer_flags && epoch_counter, "null pointer");
+  LL_CHECK_ARG(world >= 2 && world <= MAX_WORLD && rank >= 0 && rank < world, "bad rank/world (%d/%d)", rank, world);
+  LL_CHECK_ARG(n > 0 && n % 8 == 0 && ((uintptr_t)x & 15) == 0, "n must be a multiple of 8 and x 16-byte aligned");
+  TpArgs a;
+  memset(&a, 0, sizeof(a));
+  for (int r = 0; r < world; ++r) {
+    LL_CHECK_ARG(peer_parts[r] != 0 && (peer_parts[r] & 15) == 0 && peer_flags[r] != 0, "bad peer pointer for rank %d", r);
+    a.part[r] = (const __nv_bfloat16*)(uintptr_t)peer_parts[r];
+    a.flags[r] = (int32_t*)(uintptr_t)peer_flags[r];
+  }
+  static bool once = false;
+  if (!once) {
+    prefer_max_smem(tp_allreduce_add_kernel);
+    once = true;
+  }
+  tp_allreduce_add_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(a, (__nv_bfloat16*)x, epoch_counter, rank, world, n);
+  LL_LAUNCH_OK("tp_allreduce_add_kernel");
+  return LL_OK;
+}
+
+}  // extern "C"

@@ -100,6 +100,9 @@ class DecodeEngine:
         self.attn_scratch = torch.empty(N.attn_scratch_bytes(B, nh, hs, self.splits) // 4 + 16, dtype=f32, device=dev)
         self.attn_counters = torch.zeros(B * nh, dtype=i32, device=dev)
         self.graph = None
+        self.exchange = None
+        if self.tp:
+            self._setup_exchange(dev)
         self._build_args()
 
     def matches(self, B: int, max_seq_length: int) -> bool:
@@ -140,10 +143,11 @@ class DecodeEngine:
             a_attn.k_cache, a_attn.v_cache = kc.data_ptr(), vc.data_ptr()
             a_attn.n_head, a_attn.head_size, a_attn.cache_len = self.nh, cfg.head_size, self.S
             # tensor parallel: the row-parallel GEMVs store their partial sums; all-reduce, then the residual add
-            out, epi = (self.part, N.EPI_STORE) if self.tp else (self.x, N.EPI_RESIDUAL)
-            a_proj = self._gemv_args(_unwrap(blk.attn.c_proj)[0], self.att, out, epi, "proj")
+            # (the two exchanges of a block use alternating partial-sum buffers, see csrc/tp_allreduce.cu)
+            epi = N.EPI_STORE if self.tp else N.EPI_RESIDUAL
+            a_proj = self._gemv_args(_unwrap(blk.attn.c_proj)[0], self.att, self.parts[0] if self.tp else self.x, epi, "proj")
             a_fc = self._gemv_args(blk.mlp.c_fc1, self.x, self.h, N.EPI_SWIGLU, "fc", norm=blk.rms_2, lin2=blk.mlp.c_fc2)
-            a_down = self._gemv_args(_unwrap(blk.mlp.c_proj)[0], self.h, out, epi, "down")
+            a_down = self._gemv_args(_unwrap(blk.mlp.c_proj)[0], self.h, self.parts[1] if self.tp else self.x, epi, "down")
             self.layers.append((a_attn, kc, vc, a_proj, a_fc, a_down))
         self.a_head = self._gemv_args(m.lm_head, self.x, self.logits, N.EPI_STORE, "head", norm=m.transformer.ln_f)
 
@@ -162,19 +166,59 @@ class DecodeEngine:
                    N.ptr(self.attn_counters), flags, st)
             N.gemv(a_proj)
             if self.tp:
-                self._reduce_add()
+                self._reduce_add(0)
             N.gemv(a_fc)
             N.gemv(a_down)
             if self.tp:
-                self._reduce_add()
-            n += 5 + (2 if self.tp else 0)
+                self._reduce_add(1)
+            n += 5 + ((2 if self.exchange == "peer" else 4) if self.tp else 0)
         N.gemv(self.a_head)
         self.n_launches = n + 1
 
-    def _reduce_add(self):
-        """x += all_reduce(partial): the path's only exchange step (NCCL over NVLink; captured in the graph)."""
-        dist.all_reduce(self.part, op=dist.ReduceOp.SUM, group=self.tp_group)
-        N.call("ll_add", N.ptr(self.x), N.ptr(self.part), N.ptr(self.x), N.LL_BF16, self.x.numel(), N.stream())
+    def _setup_exchange(self, dev):
+        """Partial-sum buffers for the row-parallel GEMVs.  "peer" (default): two symmetric-memory buffers + a flag
+        array mapped into every rank, read by csrc/tp_allreduce.cu straight over NVLink - one small kernel per
+        exchange, capturable in the step graph.  "nccl": dist.all_reduce + ll_add, run eagerly (a captured NCCL
+        collective next to programmatic-launch kernels stalled on the 2-GPU box, profiles/r01_tp.md)."""
+        import os
+        B, E = self.x.shape
+        rank, world, group = self.model._tp
+        self.rank, self.world = rank, world
+        mode = os.environ.get("LLB200_TP_EXCHANGE", "peer")
+        if mode == "peer":
+            import torch.distributed._symmetric_memory as symm
+            grp = group if group is not None else dist.group.WORLD
+            buf = symm.empty((2, B, E), dtype=torch.bfloat16, device=dev)
+            flg = symm.empty((64,), dtype=torch.int32, device=dev)
+            buf.zero_()
+            flg.zero_()
+            hb, hf = symm.rendezvous(buf, grp), symm.rendezvous(flg, grp)
+            torch.cuda.synchronize()
+            dist.barrier(group=group)                     # every rank's flags are zero before anyone raises one
+            import ctypes as C
+            stride = B * E * 2
+            self._peer_parts = [(C.c_uint64 * world)(*[int(p) + j * stride for p in hb.buffer_ptrs]) for j in range(2)]
+            self._peer_flags = (C.c_uint64 * world)(*[int(p) for p in hf.buffer_ptrs])
+            self._symm = (buf, flg, hb, hf)
+            self.parts = [buf[0], buf[1]]
+            self.epoch = torch.zeros(1, dtype=torch.int32, device=dev)
+            self.exchange = "peer"
+        elif mode == "nccl":
+            self.parts = [self.part, self.part]
+            self.exchange = "nccl"
+            self.use_graph = False
+        else:
+            raise ValueError(f"LLB200_TP_EXCHANGE must be 'peer' or 'nccl', not {mode!r}")
+
+    def _reduce_add(self, j: int):
+        """x += sum over ranks of the partial result in buffer ``j``: the path's only exchange step."""
+        if self.exchange == "peer":
+            import ctypes as C
+            N.call("ll_tp_allreduce_add", N.ptr(self.x), C.cast(self._peer_parts[j], C.c_void_p), C.cast(self._peer_flags, C.c_void_p),
+                   N.ptr(self.epoch), self.rank, self.world, self.x.numel(), N.stream())
+        else:
+            dist.all_reduce(self.part, op=dist.ReduceOp.SUM, group=self.tp_group)
+            N.call("ll_add", N.ptr(self.x), N.ptr(self.part), N.ptr(self.x), N.LL_BF16, self.x.numel(), N.stream())
 
     def _capture(self):
         # warm up eagerly on a side stream (also sizes kernel attributes), then capture
