@@ -225,7 +225,9 @@ def main():
     sampler = ClockSampler(local) if rank == 0 else None
     NV.LAUNCHES = 0
     replays0 = model._engine.n_replays if model._engine is not None else 0
+    torch.cuda.profiler.start()        # `ncu --profile-from-start off` sees exactly the timed region
     ms_res, t0, t1 = timed(step_resident, args.steps)
+    torch.cuda.profiler.stop()
     launches = NV.LAUNCHES + (model._engine.n_replays - replays0) * model._engine.n_launches
     clocks = sampler.stop(t0, t1) if sampler else None
     for _ in range(min(args.warmup, 1)):

@@ -159,6 +159,17 @@ LL_API int ll_int8_linear(const void* x, int act_dtype, const int8_t* cb, const 
                    int N, int K, float threshold, void* workspace, size_t workspace_bytes, ll_stream stream);
 
 /* ---------------------------------------------------------------------------------------
+ * Sampling tail of generate() (ref generate.py:62-75: logits / temperature, top-k mask, softmax, multinomial) as one
+ * single-CTA kernel, bf16 logits [V].  l = bf16(logit / temperature); entries below the top_k-th largest l are dropped
+ * (ties kept; top_k <= 0 keeps all); p = bf16(softmax(l)); the token is drawn by inverse CDF in index order from the
+ * uniform number u[*step]; *step is then incremented.  The token is written to tok[0] (int64: the next step's
+ * embedding index) and, when out_tokens is not NULL, to out_tokens[pos[0] + 1].  Same distribution as the reference's
+ * torch.multinomial; a different random stream.
+ * ------------------------------------------------------------------------------------- */
+LL_API int ll_sample_topk(const void* logits, int V, float temperature, int top_k, const float* u, int32_t* step, const int32_t* pos,
+                   int64_t* out_tokens, int64_t* tok, ll_stream stream);
+
+/* ---------------------------------------------------------------------------------------
  * Tensor-parallel exchange (new: the reference is single-device, generate.py:122).  One-shot all-reduce over
  * NVLink peer memory fused with the residual add: x = bf16(x + bf16(sum over ranks of part_r)), summed in rank
  * order on every rank.  peer_parts / peer_flags: HOST arrays of `world` device pointers (symmetric-memory mappings

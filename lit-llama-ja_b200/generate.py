@@ -19,6 +19,58 @@ from lit_llama import LLaMA, HFTokenizer, Tokenizer  # noqa: E402
 from lit_llama.utils import EmptyInitOnDevice, lazy_load, llama_model_lookup  # noqa: E402
 
 
+def _generate_on_device(model, idx, max_new_tokens, max_seq_length, temperature, top_k, eos_id):
+    """The whole sampling loop on the device for the fused int4/bf16 engine: per new token ONE CUDA-graph replay of
+    [top-k draw (csrc/sampling.cu) -> advance position -> fused decode step], no host synchronisation.  Returns None
+    when the model is not eligible (then the per-op loop below runs).  Sampling semantics are the reference's
+    (generate.py:62-75) step for step; the random stream is torch's generator consumed as one uniform per token
+    instead of torch.multinomial's per-entry exponentials, so tokens differ from the reference for equal seeds."""
+    if idx.device.type != "cuda" or not model.use_fused_decode or max_new_tokens < 1 or temperature <= 0:
+        return None
+    n_prompt = idx.size(0)
+    if n_prompt + max_new_tokens > model.config.block_size + 1:
+        return None
+    model._ensure_caches(idx)
+    eng = model._fused_engine(1, max_seq_length)
+    if eng is not None:
+        eng.ensure_sample_graph(temperature, top_k)      # before the prefill: its warm-up runs scribble on the cache
+    input_pos = torch.arange(0, n_prompt, device=idx.device)
+    logits = model(idx.view(1, -1), max_seq_length, input_pos)[0, -1]
+    if eng is None or logits.dtype != torch.bfloat16 or not eng.begin_sampling(idx, logits, max_new_tokens):
+        return _sample_loop(model, idx, logits, max_new_tokens, max_seq_length, temperature, top_k, eos_id)
+    for _ in range(max_new_tokens - 1):
+        eng.sample_and_step(temperature, top_k)
+    eng.sample_last(temperature, top_k)
+    out = eng.out_tokens[: n_prompt + max_new_tokens].to(idx.dtype)
+    if eos_id is not None:   # ref generate.py:82-84: stop at the first eos; the returned slice ends before its slot
+        hit = (out[n_prompt:] == eos_id).nonzero()
+        if hit.numel():
+            out = out[: n_prompt + int(hit[0])]
+    return out
+
+
+def _sample_loop(model, idx, logits, max_new_tokens, max_seq_length, temperature, top_k, eos_id):
+    """ref: generate.py:56-89 with the prompt's logits already computed (per-op sampling, any dtype)."""
+    n_prompt = idx.size(0)
+    out = torch.empty(n_prompt + max_new_tokens, dtype=idx.dtype, device=idx.device)
+    out[:n_prompt] = idx
+    input_pos = torch.arange(0, n_prompt, device=idx.device)
+    for i in range(max_new_tokens):
+        if i > 0:
+            logits = model(out.index_select(0, input_pos).view(1, -1), max_seq_length, input_pos)[0, -1]
+        logits = logits / temperature
+        if top_k is not None:
+            kth = torch.topk(logits, min(top_k, logits.size(-1))).values[-1:]
+            logits = torch.where(logits < kth, -float("Inf"), logits)
+        probs = torch.nn.functional.softmax(logits, dim=-1)
+        nxt = torch.multinomial(probs, num_samples=1).to(dtype=idx.dtype)
+        input_pos = input_pos[-1:] + 1
+        out = out.index_copy(0, input_pos, nxt)
+        if nxt == eos_id:
+            return out[:input_pos]
+    return out
+
+
 @torch.no_grad()
 def generate(
     model: LLaMA,
@@ -38,23 +90,12 @@ def generate(
     total = n_prompt + max_new_tokens
     if max_seq_length is None:
         max_seq_length = min(total, model.config.block_size)
-    out = torch.empty(total, dtype=idx.dtype, device=idx.device)
-    out[:n_prompt] = idx
+    fast = _generate_on_device(model, idx, max_new_tokens, max_seq_length, temperature, top_k, eos_id)
+    if fast is not None:
+        return fast
     input_pos = torch.arange(0, n_prompt, device=idx.device)
-
-    for _ in range(max_new_tokens):
-        tokens = out.index_select(0, input_pos).view(1, -1)
-        logits = model(tokens, max_seq_length, input_pos)[0, -1] / temperature
-        if top_k is not None:
-            kth = torch.topk(logits, min(top_k, logits.size(-1))).values[-1:]
-            logits = torch.where(logits < kth, -float("Inf"), logits)
-        probs = torch.nn.functional.softmax(logits, dim=-1)
-        nxt = torch.multinomial(probs, num_samples=1).to(dtype=idx.dtype)
-        input_pos = input_pos[-1:] + 1
-        out = out.index_copy(0, input_pos, nxt)
-        if nxt == eos_id:
-            return out[:input_pos]  # as the reference: the slice ends before the eos slot
-    return out
+    logits = model(idx.view(1, -1), max_seq_length, input_pos)[0, -1]
+    return _sample_loop(model, idx, logits, max_new_tokens, max_seq_length, temperature, top_k, eos_id)
 
 
 def load_model(checkpoint_path: Path, quantize: Optional[str], device: torch.device, dtype: torch.dtype) -> LLaMA:

@@ -100,6 +100,10 @@ class DecodeEngine:
         self.attn_scratch = torch.empty(N.attn_scratch_bytes(B, nh, hs, self.splits) // 4 + 16, dtype=f32, device=dev)
         self.attn_counters = torch.zeros(B * nh, dtype=i32, device=dev)
         self.graph = None
+        self.sample_graphs = {}                        # (temperature, top_k) -> graph of [draw, advance, step]
+        self.out_tokens = torch.zeros(cfg.block_size + 2, dtype=torch.int64, device=dev)
+        self.u = torch.zeros(cfg.block_size + 2, dtype=f32, device=dev)
+        self.draw = torch.zeros(1, dtype=i32, device=dev)
         self.exchange = None
         if self.tp:
             self._setup_exchange(dev)
@@ -244,6 +248,63 @@ class DecodeEngine:
             self._capture()
         self.graph.replay()
         self.n_replays += 1
+
+    # ------------------------------------------------------------------ sampled decoding (generate()'s loop on the device)
+    def _draw(self, temperature: float, top_k):
+        """token ~ top-k / temperature softmax of ``self.logits`` -> ``self.tok`` and ``out_tokens[pos + 1]``."""
+        V = self.logits.shape[-1]
+        N.call("ll_sample_topk", N.ptr(self.logits), V, float(temperature), int(top_k) if top_k is not None else 0,
+               N.ptr(self.u), N.ptr(self.draw), N.ptr(self.pos), N.ptr(self.out_tokens), N.ptr(self.tok), N.stream())
+
+    def _run_sampled(self, temperature, top_k):
+        self._draw(temperature, top_k)
+        N.call("ll_advance_pos", N.ptr(self.pos), self.S, N.stream())
+        self._run_step()
+        self.n_launches += 2
+
+    def begin_sampling(self, prompt: torch.Tensor, last_logits: torch.Tensor, n_draws: int) -> bool:
+        """Device-side state for ``n_draws`` draws after a prompt of n tokens whose last logits are given:
+        tokens in ``out_tokens[:n]``, position n - 1, fresh uniforms from torch's generator."""
+        n = prompt.numel()
+        if self.B != 1 or n + n_draws > self.out_tokens.numel() or n_draws > self.u.numel():
+            return False
+        self.out_tokens[:n] = prompt
+        self.logits.copy_(last_logits.reshape(1, -1))
+        self.u[:n_draws].uniform_()
+        self.draw.zero_()
+        self.pos.copy_(torch.tensor([n - 1, (n - 1) % self.S, min(n, self.S)], dtype=torch.int32), non_blocking=True)
+        return True
+
+    def ensure_sample_graph(self, temperature: float, top_k):
+        """Capture [draw, advance, step] for these sampling parameters.  MUST run before the prompt is prefilled:
+        the warm-up runs write a K/V row at slot 0 and overwrite ``logits`` (the prefill then rewrites the row)."""
+        key = (float(temperature), top_k)
+        if not self.use_graph or key in self.sample_graphs:
+            return
+        if self.graph is None:
+            self._capture()
+        # run the two extra kernels once outside capture (their first launch loads them)
+        self.pos.zero_()
+        self._draw(temperature, top_k)
+        N.call("ll_advance_pos", N.ptr(self.pos), self.S, N.stream())
+        self.pos.zero_()
+        self.draw.zero_()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._run_sampled(temperature, top_k)
+        self.sample_graphs[key] = g
+
+    def sample_and_step(self, temperature: float, top_k):
+        """Draw the next token from the current logits, append it, run the decode step on it (one graph replay)."""
+        if not self.use_graph:
+            self._run_sampled(temperature, top_k)
+            return
+        self.sample_graphs[(float(temperature), top_k)].replay()   # KeyError: ensure_sample_graph() was not called
+        self.n_replays += 1
+
+    def sample_last(self, temperature: float, top_k):
+        self._draw(temperature, top_k)
 
     def forward_token(self, idx: torch.Tensor, input_pos: torch.Tensor) -> torch.Tensor:
         """``LLaMA.forward(idx[B,1], max_seq_length, input_pos[1])`` (ref: model.py:84-128)."""

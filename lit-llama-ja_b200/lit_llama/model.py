@@ -244,6 +244,14 @@ class LLaMA(nn.Module):
         n = self.config.block_size
         return torch.ones((n, n), device=idx.device, dtype=torch.bool).tril_()[None, None]
 
+    def _ensure_caches(self, idx: torch.Tensor) -> None:
+        """ref: model.py:100-103 - the RoPE and mask tables are built on first use, from ``idx``'s dtype and device."""
+        if self.rope_cache is None:
+            self.rope_cache = self.build_rope_cache(idx)
+            self._rope_f32 = self.rope_cache.float().contiguous()
+        if self.mask_cache is None:
+            self.mask_cache = self.build_mask_cache(idx)
+
     def reset_cache(self) -> None:
         self.kv_caches.clear()
         if self._engine is not None:
@@ -261,11 +269,7 @@ class LLaMA(nn.Module):
         assert max_seq_length <= block_size, f"Cannot attend to {max_seq_length}, block size is only {block_size}"
         assert T <= block_size, f"Cannot forward sequence of length {T}, block size is only {block_size}"
 
-        if self.rope_cache is None:
-            self.rope_cache = self.build_rope_cache(idx)
-            self._rope_f32 = self.rope_cache.float().contiguous()
-        if self.mask_cache is None:
-            self.mask_cache = self.build_mask_cache(idx)
+        self._ensure_caches(idx)
 
         use_cache = input_pos is not None
         if use_cache and T == 1 and self.use_fused_decode:

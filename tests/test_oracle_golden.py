@@ -148,3 +148,28 @@ def test_tiny_model_rtn_group32(golden, dt):
     if dt == "fp32":
         m.reset_cache()
         assert np.array_equal(OM.generate(m, g["idx"][0, :8], 12, top_k=1), g["rtn32.fp32.generate_top1"])
+
+
+def test_sampling_oracle_matches_torch_ops_of_the_reference():
+    """oracle/sampling.probabilities == the reference's own op sequence (generate.py:62-69) run with torch on CPU
+    in bf16 and fp32: same kept set, probabilities within one bf16 ulp (the softmax's exp differs in the last bit)."""
+    import torch
+    from oracle import sampling as OS
+    from oracle import quant as OQ
+
+    r = np.random.RandomState(11)
+    for V, k, T in ((32000, 200, 0.8), (1000, 1, 1.0), (4096, None, 1.3), (777, 50, 0.5)):
+        logits = OQ.bf16_round(r.randn(V).astype(np.float32) * 3.0)
+        logits[r.randint(0, V, 5)] = logits.max()          # ties at the top
+        t = torch.from_numpy(logits).to(torch.bfloat16) / T
+        if k is not None:
+            v, _ = torch.topk(t, min(k, t.size(-1)))
+            t = torch.where(t < v[[-1]], -float("Inf"), t)
+        want = torch.nn.functional.softmax(t, dim=-1).float().numpy()
+        got = OS.probabilities(logits, T, k, "bf16")
+        assert np.array_equal(got > 0, want > 0)
+        assert np.all(np.abs(got - want) <= np.maximum(want, got) * 2.0**-7)
+        assert (got != want).mean() < 0.05
+    p = OS.probabilities(logits, 0.5, 50)
+    counts = np.bincount([OS.draw(p, u) for u in (np.arange(4000) + 0.5) / 4000], minlength=p.size)
+    assert np.abs(counts / 4000 - p / p.sum()).max() < 1e-3     # inverse CDF reproduces the distribution
