@@ -30,7 +30,7 @@ __device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
 }
 __device__ __forceinline__ uint4 ld_relaxed_sys_v4(const void* p) {
   uint4 v;
-  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
   return v;
 }
 
@@ -38,6 +38,9 @@ __global__ void __launch_bounds__(1024) tp_allreduce_add_kernel(const __grid_con
                                                                 int32_t* __restrict__ epoch_counter, int rank, int world, int n) {
   __shared__ int s_epoch;
   if (threadIdx.x == 0) s_epoch = ++(*epoch_counter);  // same call count on every rank -> same epoch
+  // the local residual vector does not depend on the peers: fetched while the flags travel
+  uint4 x_first = make_uint4(0u, 0u, 0u, 0u);
+  if (threadIdx.x * 8 < n) x_first = *reinterpret_cast<const uint4*>(x + threadIdx.x * 8);
   __syncthreads();
   const int epoch = s_epoch;
   // announce: "my partial sums of this epoch are in my buffer" (written by the previous kernel of this stream)
@@ -51,16 +54,25 @@ __global__ void __launch_bounds__(1024) tp_allreduce_add_kernel(const __grid_con
   __syncthreads();
   for (int i = threadIdx.x * 8; i < n; i += blockDim.x * 8) {
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int r = 0; r < world; ++r) {
-      const uint4 v = ld_relaxed_sys_v4(a.part[r] + i);
-      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    // all peers' vectors are requested before any is used: one NVLink round trip, not `world` of them
+    for (int r0 = 0; r0 < world; r0 += 8) {
+      uint4 v[8];
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        acc[2 * e] += bf16_bits_to_f32(w[e] & 0xffffu);
-        acc[2 * e + 1] += bf16_bits_to_f32(w[e] >> 16);
+      for (int j = 0; j < 8; ++j) {
+        v[j] = make_uint4(0u, 0u, 0u, 0u);
+        if (r0 + j < world) v[j] = ld_relaxed_sys_v4(a.part[r0 + j] + i);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {  // rank order; absent ranks add +0
+        const uint32_t w[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          acc[2 * e] += bf16_bits_to_f32(w[e] & 0xffffu);
+          acc[2 * e + 1] += bf16_bits_to_f32(w[e] >> 16);
+        }
       }
     }
-    const uint4 xv = *reinterpret_cast<const uint4*>(x + i);
+    const uint4 xv = i == threadIdx.x * 8 ? x_first : *reinterpret_cast<const uint4*>(x + i);
     const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
     uint32_t o[4];
 #pragma unroll

@@ -97,6 +97,9 @@ class DecodeEngine:
 
         nh, hs = self.nh, cfg.head_size
         self.splits = max(1, min(16, (2 * N._fn["ll_sm_count"]()) // max(1, B * nh), (max_seq_length + 63) // 64))
+        import os
+        if os.environ.get("LLB200_ATTN_SPLITS"):
+            self.splits = int(os.environ["LLB200_ATTN_SPLITS"])
         self.attn_scratch = torch.empty(N.attn_scratch_bytes(B, nh, hs, self.splits) // 4 + 16, dtype=f32, device=dev)
         self.attn_counters = torch.zeros(B * nh, dtype=i32, device=dev)
         self.graph = None
