@@ -159,6 +159,17 @@ LL_API int ll_int8_linear(const void* x, int act_dtype, const int8_t* cb, const 
                    int N, int K, float threshold, void* workspace, size_t workspace_bytes, ll_stream stream);
 
 /* ---------------------------------------------------------------------------------------
+ * GPTQ solver, one block of <= 128 columns (ref GPTQQuantizer.quantize, quantization.py:559-590; fp32).
+ * W [N][ldw] working weights (columns i1 .. i1+count-1 are read), Hinv [K][ldh] upper Cholesky factor of the inverse
+ * Hessian, scales/zeros [N][G] (read for groupsize == -1; written at group starts otherwise - the reference's grouped
+ * branch raises at 573-577, its evident intent is implemented), Q [N][ldq] receives the on-grid weights of the block's
+ * columns, Err [N][count] the scaled errors for the caller's cross-block update W[:, i2:] -= Err @ Hinv[i1:i2, i2:],
+ * loss[N] += sum_i (w - q)^2 / d^2.  Same fp32 operation order as the reference: identical codes for identical Hinv.
+ * ------------------------------------------------------------------------------------- */
+LL_API int ll_gptq_block(float* W, int ldw, const float* Hinv, int ldh, float* scales, float* zeros, int G, float* Q, int ldq,
+                  float* Err, float* loss, int N, int i1, int count, int groupsize, int maxq, ll_stream stream);
+
+/* ---------------------------------------------------------------------------------------
  * Sampling tail of generate() (ref generate.py:62-75: logits / temperature, top-k mask, softmax, multinomial) as one
  * single-CTA kernel, bf16 logits [V].  l = bf16(logit / temperature); entries below the top_k-th largest l are dropped
  * (ties kept; top_k <= 0 keeps all); p = bf16(softmax(l)); the token is drawn by inverse CDF in index order from the

@@ -65,6 +65,7 @@ EXPORTS = {
     "ll_int8_quantize_weight": ([vp, i32, vp, vp, i32, i32, vp], C.c_int),
     "ll_int8_workspace_bytes": ([i32, i32, i32], sz_t),
     "ll_int8_linear": ([vp, i32, vp, vp, vp, vp, i32, i32, i32, C.c_float, vp, sz_t, vp], C.c_int),
+    "ll_gptq_block": ([vp, i32, vp, i32, vp, vp, i32, vp, i32, vp, vp, i32, i32, i32, i32, i32, vp], C.c_int),
     "ll_sample_topk": ([vp, i32, C.c_float, i32, vp, vp, vp, vp, vp, vp], C.c_int),
     "ll_tp_allreduce_add": ([vp, vp, vp, vp, i32, i32, i32, vp], C.c_int),
     "ll_rmsnorm": ([vp, vp, vp, i32, i32, i32, C.c_float, vp], C.c_int),

@@ -301,7 +301,9 @@ def find_params_weight(x: torch.Tensor, maxq: int):
     dead = (xmin == 0) & (xmax == 0)
     xmin = torch.where(dead, torch.full_like(xmin, -1), xmin)
     xmax = torch.where(dead, torch.full_like(xmax, +1), xmax)
-    scale = (xmax - xmin) / maxq
+    # a tensor divisor: torch's CUDA kernels turn division by a Python scalar into a multiplication by its
+    # reciprocal (1 ulp off the reference's CPU result); tensor / tensor is IEEE division
+    scale = (xmax - xmin) / torch.full_like(xmax, float(maxq))
     zero = torch.round(-xmin / scale)
     return scale.reshape(-1, 1), zero.reshape(-1, 1)
 
@@ -332,3 +334,144 @@ def rtn_quantize_(lin: ColBlockQuantizedLinear, weight: torch.Tensor) -> ColBloc
     q = quantize_weight(wg, s_st, z_st, maxq).view(n, k)
     lin.pack_weight(q.to(lin.scales.dtype))
     return lin
+
+
+# --------------------------------------------------------------------------------------- row Z2: the GPTQ solver
+@torch.no_grad()
+def gptq_solve(W: torch.Tensor, Hinv: torch.Tensor, scales: torch.Tensor, zeros: torch.Tensor, *, bits: int,
+               blocksize: int = 128, groupsize: int = -1):
+    """The column walk of ``GPTQQuantizer.quantize`` (ref quantization.py:559-592) on the device.
+
+    ``W`` [N, K] fp32 (modified in place), ``Hinv`` [K, K] fp32 upper Cholesky factor of the inverse Hessian,
+    ``scales`` / ``zeros`` [N, G] fp32 (per-row parameters are read, group parameters are written).  Per block of
+    ``blocksize`` columns one kernel (``ll_gptq_block``) walks the columns in the reference's order; the cross-block
+    update is a plain GEMM.  Returns ``(Q, loss_per_row)``: on-grid weights [N, K] and sum of Losses per row."""
+    N.require_cuda(W, Hinv, scales, zeros)
+    assert W.dtype == Hinv.dtype == scales.dtype == zeros.dtype == torch.float32
+    assert W.is_contiguous() and Hinv.is_contiguous() and scales.is_contiguous() and zeros.is_contiguous()
+    rows, columns = W.shape
+    if blocksize > 128:
+        raise ValueError("gptq_solve: blocksize must be <= 128")
+    if groupsize != -1 and (blocksize % groupsize != 0 or columns % groupsize != 0):
+        raise ValueError("gptq_solve: groupsize must be -1 or divide blocksize and the column count")
+    Q = torch.zeros_like(W)
+    loss = torch.zeros(rows, dtype=torch.float32, device=W.device)
+    G = scales.shape[1]
+    for i1 in range(0, columns, blocksize):
+        i2 = min(i1 + blocksize, columns)
+        count = i2 - i1
+        err = torch.empty((rows, count), dtype=torch.float32, device=W.device)
+        N.call("ll_gptq_block", N.ptr(W), columns, N.ptr(Hinv), columns, N.ptr(scales), N.ptr(zeros), G, N.ptr(Q), columns,
+               N.ptr(err), N.ptr(loss), rows, i1, count, groupsize, 2 ** bits - 1, N.stream())
+        if i2 < columns:
+            W[:, i2:] -= err @ Hinv[i1:i2, i2:]           # ref 592 (cuBLAS: a plain GEMM)
+    return Q, loss / 2                                     # ref 590: Losses1 / 2
+
+
+class GPTQQuantizer:
+    """ref: lit_llama/quantization.py:424-614 (E. Frantar et al., GPTQ, arXiv:2210.17323) - same constructor,
+    ``collect_input_stats`` forward-hook signature and ``quantize() -> (ColBlockQuantizedLinear, error)``.
+
+    B200-native: the Hessian accumulates on the device (one GEMM per calibration batch), the damped inverse and its
+    Cholesky factor come from cuSOLVER (torch.linalg), and the column walk runs as one kernel per 128-column block
+    (``gptq_solve``) instead of one Python iteration per column.  The reference's ``groupsize != -1`` branch raises
+    (573-577 assigns a [rows, 1] tensor into a [rows] slice); here the group's parameters are stored in column
+    ``g`` as that code intends, so group-128 checkpoints can actually be written.  CUDA only."""
+
+    def __init__(self, linear_module, *, bits, perchannel=True, sym=False, blocksize=128, percdamp=0.01, groupsize=-1,
+                 actorder=False):
+        assert isinstance(linear_module, torch.nn.Linear)
+        self.linear_module = linear_module
+        self.dev = linear_module.weight.device
+        N.require_cuda(linear_module.weight)
+        self.rows, self.columns = linear_module.weight.shape
+        self.H = torch.zeros((self.columns, self.columns), device=self.dev)
+        self.nsamples = 0
+        self.bits = bits
+        self.maxq = 2 ** bits - 1
+        self.perchannel = perchannel
+        self.sym = sym
+        self.blocksize = blocksize
+        self.percdamp = percdamp
+        self.groupsize = groupsize
+        self.actorder = actorder
+        self.tile_cols = self.columns if groupsize == -1 else groupsize
+        self.scales = torch.zeros((self.rows, (self.columns + self.tile_cols - 1) // self.tile_cols),
+                                  dtype=linear_module.weight.dtype, device=self.dev)
+        self.zeros = torch.zeros_like(self.scales)
+        assert not (self.actorder and self.groupsize != -1), "The permutation trick does not work for grouped quantization"
+        if not perchannel or sym:
+            raise NotImplementedError("only the reference's defaults (perchannel=True, sym=False) are on the path")
+
+    @staticmethod
+    def quantize_weight(x, scale, zero, maxq):
+        return quantize_weight(x, scale, zero, maxq)
+
+    def find_params_weight(self, x):
+        return find_params_weight(x, self.maxq)
+
+    @torch.no_grad()
+    def collect_input_stats(self, _1, inp, _2):
+        """ref 513-527: running mean of 2 x x^T over the calibration batches (a forward hook)."""
+        inp = inp[0].detach()
+        self.last_inp = inp
+        if inp.dim() == 2:
+            inp = inp.unsqueeze(0)
+        tmp = inp.shape[0]
+        if inp.dim() == 3:
+            inp = inp.reshape((-1, inp.shape[-1]))
+        inp = inp.t()
+        self.H *= self.nsamples / (self.nsamples + tmp)
+        self.nsamples += tmp
+        inp = math.sqrt(2 / self.nsamples) * inp.float()
+        self.H += inp.matmul(inp.t())
+
+    @torch.no_grad()
+    def quantize(self):
+        """ref 529-614."""
+        W = self.linear_module.weight.detach().to(dtype=torch.float, copy=True)
+        scale, zero = self.find_params_weight(W)
+        scales = torch.zeros(self.scales.shape, dtype=torch.float32, device=self.dev)
+        zeros = torch.zeros_like(scales)
+        scales[:] = scale
+        zeros[:] = zero
+
+        H = self.H
+        del self.H
+        dead = torch.diag(H) == 0
+        H[dead, dead] = 1
+        W[:, dead] = 0
+        if self.actorder:
+            perm = torch.argsort(torch.diag(H), descending=True)
+            W = W[:, perm].contiguous()
+            H = H[perm][:, perm]
+        damp = self.percdamp * torch.mean(torch.diag(H))
+        diag = torch.arange(self.columns, device=self.dev)
+        H[diag, diag] += damp
+        H = torch.linalg.cholesky(H)
+        H = torch.cholesky_inverse(H)
+        Hinv = torch.linalg.cholesky(H, upper=True).contiguous()
+
+        Q, loss = gptq_solve(W.contiguous(), Hinv, scales, zeros, bits=self.bits, blocksize=self.blocksize,
+                             groupsize=self.groupsize)
+        if self.actorder:
+            Q = Q[:, torch.argsort(perm)]
+        weight = Q.reshape(self.linear_module.weight.shape).to(self.linear_module.weight.data.dtype)
+        error = torch.sum(loss).item()
+
+        self.scales.copy_(scales)
+        self.zeros.copy_(zeros)
+        prev = torch.get_default_dtype()
+        wd = self.linear_module.weight.dtype
+        torch.set_default_dtype(wd if wd.is_floating_point else prev)
+        try:
+            q_module = ColBlockQuantizedLinear(self.linear_module.in_features, self.linear_module.out_features,
+                                               self.linear_module.bias is not None, bits=self.bits,
+                                               tile_cols=self.groupsize).to(self.dev)
+        finally:
+            torch.set_default_dtype(prev)
+        q_module.scales = self.scales
+        q_module.zeros = self.zeros
+        q_module.pack_weight(weight)
+        q_module.bias = self.linear_module.bias
+        return q_module, error

@@ -194,15 +194,33 @@ def gptq_hessian(inputs) -> tuple[np.ndarray, int]:
     return H, nsamples
 
 
-def gptq_quantize(W, H, bits: int, blocksize: int = 128, percdamp: float = 0.01,
-                  groupsize: int = -1, actorder: bool = False):
-    """GPTQQuantizer.quantize, quantization.py:529-614, float32 throughout.
-
-    Returns (Q_on_grid[N,K], scales[N,G], zeros[N,G], error).  For ``groupsize != -1``
-    the reference raises at 573-577 (it assigns a [rows,1] tensor into a [rows] slice);
-    the evident intent - store the group's params in column ``g`` - is restated here."""
+def gptq_hinv(H, percdamp: float = 0.01) -> np.ndarray:
+    """quantization.py:549-555: damp the diagonal by ``percdamp * mean(diag H)``, then
+    ``cholesky -> cholesky_inverse -> cholesky(upper=True)`` in float32 (LAPACK spotrf / spotri)."""
     from scipy.linalg import lapack
 
+    H = np.array(H, dtype=F32, copy=True)
+    columns = H.shape[0]
+    damp = F32(percdamp) * np.mean(np.diag(H)).astype(F32)
+    H[np.arange(columns), np.arange(columns)] += damp
+    L, info = lapack.spotrf(H, lower=1)
+    assert info == 0
+    Hinv, info = lapack.spotri(L, lower=1)
+    assert info == 0
+    Hinv = np.tril(Hinv) + np.tril(Hinv, -1).T
+    U, info = lapack.spotrf(Hinv.astype(F32), lower=0)
+    assert info == 0
+    return np.triu(U).astype(F32)
+
+
+def gptq_quantize(W, H, bits: int, blocksize: int = 128, percdamp: float = 0.01,
+                  groupsize: int = -1, actorder: bool = False, return_hinv: bool = False):
+    """GPTQQuantizer.quantize, quantization.py:529-614, float32 throughout.
+
+    Returns (Q_on_grid[N,K], scales[N,G], zeros[N,G], error) (+ the Hinv factor and the permuted working W the
+    column walk started from, when ``return_hinv``).  For ``groupsize != -1``
+    the reference raises at 573-577 (it assigns a [rows,1] tensor into a [rows] slice);
+    the evident intent - store the group's params in column ``g`` - is restated here."""
     W = np.array(W, dtype=F32, copy=True)
     H = np.array(H, dtype=F32, copy=True)
     rows, columns = W.shape
@@ -225,16 +243,8 @@ def gptq_quantize(W, H, bits: int, blocksize: int = 128, percdamp: float = 0.01,
         H = H[perm][:, perm]
     Losses = np.zeros_like(W)
     Q = np.zeros_like(W)
-    damp = F32(percdamp) * np.mean(np.diag(H)).astype(F32)
-    H[np.arange(columns), np.arange(columns)] += damp
-    L, info = lapack.spotrf(H, lower=1)
-    assert info == 0
-    Hinv, info = lapack.spotri(L, lower=1)
-    assert info == 0
-    Hinv = np.tril(Hinv) + np.tril(Hinv, -1).T
-    U, info = lapack.spotrf(Hinv.astype(F32), lower=0)
-    assert info == 0
-    Hinv = np.triu(U).astype(F32)
+    Hinv = gptq_hinv(H, percdamp)
+    W_start = W.copy()
 
     for i1 in range(0, columns, blocksize):
         i2 = min(i1 + blocksize, columns)
@@ -261,6 +271,8 @@ def gptq_quantize(W, H, bits: int, blocksize: int = 128, percdamp: float = 0.01,
         W[:, i2:] -= Err1 @ Hinv[i1:i2, i2:]
     if actorder:
         Q = Q[:, np.argsort(perm, kind="stable")]
+    if return_hinv:
+        return Q, scales, zeros, float(Losses.sum()), Hinv, W_start
     return Q, scales, zeros, float(Losses.sum())
 
 
