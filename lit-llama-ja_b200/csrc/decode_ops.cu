@@ -160,22 +160,34 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
   for (int e = 0; e < EPL; ++e) o[e] = 0.f;
   const T* kbase = kc + (size_t)bh * S * HS + li * EPL;
   const T* vbase = vc + (size_t)bh * S * HS + li * EPL;
-  for (int s = s0 + warp * 4 + lg; s < s1; s += 4 * NW) {
-    float kr[EPL], vr[EPL];
-    vec_ld<T>::template ld<EPL>(kbase + (size_t)s * HS, kr);
-    vec_ld<T>::template ld<EPL>(vbase + (size_t)s * HS, vr);
-    float sc = 0.f;
+  // R rows of K and V per lane group are requested before any of them is used: one memory round trip per R * 16
+  // positions of the CTA instead of one per 16 (the loop was latency-bound: 5 dependent trips at 640 positions)
+  constexpr int R = 5;
+  for (int sb = s0 + warp * 4 + lg; sb < s1; sb += 4 * NW * R) {
+    float kr[R][EPL], vr[R][EPL];
 #pragma unroll
-    for (int e = 0; e < EPL; ++e) sc = fmaf(qr[e], kr[e], sc);
-    sc += __shfl_xor_sync(gmask, sc, 1);   // the 8 lanes of a group share a trip count; groups do not
-    sc += __shfl_xor_sync(gmask, sc, 2);
-    sc += __shfl_xor_sync(gmask, sc, 4);
-    const float mn = fmaxf(m, sc);
-    const float corr = exp2f(m - mn), pr = exp2f(sc - mn);
-    l = l * corr + pr;
+    for (int r = 0; r < R; ++r) {
+      const int s = min(sb + r * 4 * NW, s1 - 1);  // clamped rows are loaded but not used
+      vec_ld<T>::template ld<EPL>(kbase + (size_t)s * HS, kr[r]);
+      vec_ld<T>::template ld<EPL>(vbase + (size_t)s * HS, vr[r]);
+    }
 #pragma unroll
-    for (int e = 0; e < EPL; ++e) o[e] = o[e] * corr + pr * vr[e];
-    m = mn;
+    for (int r = 0; r < R; ++r) {
+      float sc = 0.f;
+#pragma unroll
+      for (int e = 0; e < EPL; ++e) sc = fmaf(qr[e], kr[r][e], sc);
+      sc += __shfl_xor_sync(gmask, sc, 1);   // the 8 lanes of a group share a trip count; groups do not
+      sc += __shfl_xor_sync(gmask, sc, 2);
+      sc += __shfl_xor_sync(gmask, sc, 4);
+      if (sb + r * 4 * NW < s1) {
+        const float mn = fmaxf(m, sc);
+        const float corr = exp2f(m - mn), pr = exp2f(sc - mn);
+        l = l * corr + pr;
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) o[e] = o[e] * corr + pr * vr[r][e];
+        m = mn;
+      }
+    }
   }
   // combine the 16 (warp, lane-group) partial states of this CTA in fixed order
   if (li == 0) { s_m[warp * 4 + lg] = m; s_l[warp * 4 + lg] = l; }
