@@ -309,9 +309,21 @@ def kernel_metrics(model, device):
     e1.record(); torch.cuda.synchronize()
     tok_ms = e0.elapsed_time(e1) / reps
     _, kv = algorithmic_bytes(model, pos_avg)
+    # DRAM traffic per launch from the committed `ncu --set full` capture of this kernel (profiles/): the four
+    # per-layer launches measured, the lm_head taken at its algorithmic bytes; None if the capture is not there
+    traffic = None
+    tpath = ROOT / "profiles" / "r01_gemv_traffic.json"
+    if tpath.exists() and model.config.n_layer == 32 and model.config.n_embd == 4096:
+        t = json.loads(tpath.read_text())
+        per_layer = sum(t["dram_read_bytes"].values())
+        head_mod = model.lm_head
+        head = (head_mod.out_features * head_mod.in_features // 2
+                + 4 * head_mod.out_features * (head_mod.in_features // head_mod.tile_cols)
+                + 2 * (head_mod.out_features + head_mod.in_features))
+        traffic = (32 * per_layer + head) / n_gemv
     return {
         "roofline": {"bound": "hbm", "kernel": "gemv_int4_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": wbytes / n_gemv, "avg_launch_us": 1e3 * gemv_ms / n_gemv,
                      "launches_per_token": n_gemv},
         "decode_step": {"ms_per_token": tok_ms, "tokens_per_s": 1e3 / tok_ms, "position": pos_avg,
