@@ -2,6 +2,8 @@
 // RoPE + in-place KV-cache write, split-KV decode attention, SwiGLU product, residual add.
 // ref: /root/reference/lit_llama/model.py:110, 162-175, 192-243, 257-260, 276-283, 312-329.
 // Every kernel mirrors torch's rounding points (each elementwise op rounds to the activation dtype).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace llb {
@@ -127,7 +129,9 @@ template <> struct vec_ld<float> {
   }
 };
 
-template <typename T, int HS>
+// CL: the splits of one (batch, head) form a thread-block cluster (nsplit <= 8) and hand their partial states to the
+// cluster's first CTA through distributed shared memory - no global scratch, fence, atomic or reload on the way.
+template <typename T, int HS, bool CL>
 __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ q, const T* __restrict__ kc,
                                                           const T* __restrict__ vc, const int32_t* __restrict__ pos,
                                                           T* __restrict__ y, int n_head, int S, int nsplit,
@@ -137,6 +141,7 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
   constexpr int NW = 4;
   __shared__ float s_m[NW * 4], s_l[NW * 4];
   __shared__ float s_o[NW * 4][HS];
+  __shared__ float c_st[CL ? 8 : 1][HS + 2];  // leader CTA: (M, L, O[HS]) of every split
   __shared__ int s_last;
   if (use_pdl) {
     pdl_launch_dependents();
@@ -162,7 +167,7 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
   const T* vbase = vc + (size_t)bh * S * HS + li * EPL;
   // R rows of K and V per lane group are requested before any of them is used: one memory round trip per R * 16
   // positions of the CTA instead of one per 16 (the loop was latency-bound: 5 dependent trips at 640 positions)
-  constexpr int R = 5;
+  constexpr int R = 6;
   for (int sb = s0 + warp * 4 + lg; sb < s1; sb += 4 * NW * R) {
     float kr[R][EPL], vr[R][EPL];
 #pragma unroll
@@ -210,9 +215,40 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
     }
     if (nsplit == 1) {
       dt<T>::st(y + (size_t)bh * HS, threadIdx.x, O / L);
+    } else if constexpr (CL) {
+      // write this split's state into the leader's shared memory (cluster rank 0 = split 0)
+      uint32_t remote;
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(&c_st[split][0])), "r"(0));
+      asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote + 4u * (2 + threadIdx.x)), "f"(O) : "memory");
+      if (threadIdx.x == 0) {
+        asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(M) : "memory");
+        asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote + 4u), "f"(L) : "memory");
+      }
     } else {
       my[2 + threadIdx.x] = O;
       if (threadIdx.x == 0) { my[0] = M; my[1] = L; }
+    }
+  }
+  if constexpr (CL) {
+    if (nsplit > 1) {
+      asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+      asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+      if (split != 0) return;
+      if (threadIdx.x < HS) {
+        float M = -INFINITY;
+        for (int i = 0; i < nsplit; ++i) M = fmaxf(M, c_st[i][0]);
+        float L = 0.f, O = 0.f;
+        for (int i = 0; i < nsplit; ++i) {  // split order: deterministic
+          const float mi = c_st[i][0];
+          if (mi > -INFINITY) {
+            const float c = exp2f(mi - M);
+            L += c_st[i][1] * c;
+            O += c_st[i][2 + threadIdx.x] * c;
+          }
+        }
+        dt<T>::st(y + (size_t)bh * HS, threadIdx.x, O / L);
+      }
+      return;
     }
   }
   if (nsplit == 1) return;
@@ -343,19 +379,41 @@ int ll_decode_attn(const void* q, const void* k_cache, const void* v_cache, cons
                    int flags, ll_stream stream) {
   LL_CHECK_ARG(q && k_cache && v_cache && pos && y, "null pointer");
   LL_CHECK_ARG(B > 0 && n_head > 0 && cache_len > 0 && max_splits >= 1 && max_splits <= 64, "bad shape");
-  if (max_splits > 1) LL_CHECK_ARG(scratch && counters, "split decode attention needs scratch and counters");
+  if (max_splits > 8) LL_CHECK_ARG(scratch && counters, "decode attention with more than 8 splits needs scratch and counters");
   dim3 grid(B * n_head, max_splits), block(128);
   cudaStream_t st = (cudaStream_t)stream;
   const bool pdl = (flags & LL_GEMV_PDL) != 0;
+  // 2..8 splits: one cluster per (batch, head), partial states exchanged through distributed shared memory
+  static int use_cluster = -1;
+  if (use_cluster < 0) {
+    const char* e = getenv("LLB200_ATTN_CLUSTER");
+    use_cluster = (e && atoi(e) == 0) ? 0 : 1;
+  }
+  const bool cl = use_cluster && max_splits >= 2 && max_splits <= 8;
 #define ATTN(TT, HS)                                                                                              \
   do {                                                                                                            \
     static bool once = false;                                                                                     \
     if (!once) {                                                                                                  \
-      prefer_max_smem(decode_attn_kernel<TT, HS>);                                                                \
+      prefer_max_smem(decode_attn_kernel<TT, HS, false>);                                                         \
+      prefer_max_smem(decode_attn_kernel<TT, HS, true>);                                                          \
       once = true;                                                                                                \
     }                                                                                                             \
-    LL_CUDA(launch(decode_attn_kernel<TT, HS>, grid, block, 0, st, pdl, (const TT*)q, (const TT*)k_cache,        \
-                   (const TT*)v_cache, pos, (TT*)y, n_head, cache_len, max_splits, scratch, counters, pdl ? 1 : 0)); \
+    if (cl) {                                                                                                     \
+      cudaLaunchConfig_t cfg{};                                                                                   \
+      cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = 0; cfg.stream = st;                        \
+      cudaLaunchAttribute attr[2];                                                                                \
+      attr[0].id = cudaLaunchAttributeClusterDimension;                                                           \
+      attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = (unsigned)max_splits; attr[0].val.clusterDim.z = 1; \
+      attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;                                            \
+      attr[1].val.programmaticStreamSerializationAllowed = 1;                                                     \
+      cfg.attrs = attr; cfg.numAttrs = pdl ? 2 : 1;                                                               \
+      LL_CUDA(cudaLaunchKernelEx(&cfg, decode_attn_kernel<TT, HS, true>, (const TT*)q, (const TT*)k_cache,        \
+                                 (const TT*)v_cache, pos, (TT*)y, n_head, cache_len, max_splits, scratch, counters, \
+                                 pdl ? 1 : 0));                                                                   \
+    } else {                                                                                                      \
+      LL_CUDA(launch(decode_attn_kernel<TT, HS, false>, grid, block, 0, st, pdl, (const TT*)q, (const TT*)k_cache, \
+                     (const TT*)v_cache, pos, (TT*)y, n_head, cache_len, max_splits, scratch, counters, pdl ? 1 : 0)); \
+    }                                                                                                             \
   } while (0)
   if (dtype == LL_BF16) {
     if (head_size == 128) ATTN(__nv_bfloat16, 128);

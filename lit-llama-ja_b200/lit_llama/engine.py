@@ -96,7 +96,7 @@ class DecodeEngine:
         self.n_replays = 0
 
         nh, hs = self.nh, cfg.head_size
-        self.splits = max(1, min(16, (2 * N._fn["ll_sm_count"]()) // max(1, B * nh), (max_seq_length + 63) // 64))
+        self.splits = max(1, min(8, (2 * N._fn["ll_sm_count"]()) // max(1, B * nh), (max_seq_length + 63) // 64))   # <= 8: one cluster per head
         import os
         if os.environ.get("LLB200_ATTN_SPLITS"):
             self.splits = int(os.environ["LLB200_ATTN_SPLITS"])

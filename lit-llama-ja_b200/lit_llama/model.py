@@ -147,7 +147,7 @@ class CausalSelfAttention(nn.Module):
                N.ptr(k_cache), N.ptr(v_cache), N.dtype_code(x.dtype), B, T, nh, hs, S, N.stream())
         if step.use_cache and T == 1 and hs in (32, 64, 128):
             y = torch.empty((B, 1, C), device=x.device, dtype=x.dtype)
-            splits = max(1, min(16, (2 * N._fn["ll_sm_count"]()) // max(1, B * nh), (S + 63) // 64))
+            splits = max(1, min(8, (2 * N._fn["ll_sm_count"]()) // max(1, B * nh), (S + 63) // 64))
             ws = N.Workspace.get(x.device).ensure(attn_bytes=N.attn_scratch_bytes(B, nh, hs, splits),
                                                   attn_counters=B * nh)
             N.call("ll_decode_attn", N.ptr(q), N.ptr(k_cache), N.ptr(v_cache), N.ptr(step.pos3), N.ptr(y),
