@@ -40,7 +40,7 @@ def timed_graph(fn, reps=20):
     return 1e3 * e0.elapsed_time(e1) / reps
 
 
-for pdl, apdl in ((True, False),):
+for pdl, apdl in ((True, os.environ.get("PROBE_APDL", "0") == "1"),):
     os.environ["LLB200_PDL"] = "1" if pdl else "0"
     os.environ["LLB200_PDL_ATTN"] = "1" if apdl else "0"
     model.kv_caches.clear(); model._engine = None
