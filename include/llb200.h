@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define LL_ABI_VERSION 3
+#define LL_ABI_VERSION 4
 
 #define LL_OK 0
 #define LL_ERR_ARG (-1)         /* bad shape / dtype / null pointer */
@@ -102,6 +102,7 @@ LL_API int ll_int4_prepare(const uint8_t* qw, const void* scales, const void* ze
 #define LL_EPI_RESIDUAL 1 /* y (residual stream, in place) = bf16(y + bf16(acc)) */
 #define LL_EPI_ROPE_KV 2  /* c_attn: RoPE on q,k; q -> y, k,v -> KV cache at pos[1] */
 #define LL_EPI_SWIGLU 3   /* y = bf16(bf16(silu(bf16(accA))) * bf16(accB)), accB from w2 */
+#define LL_EPI_PUSH 4     /* y_r[M][N] = x . W^T on every rank r (peer stores) + arrival counters, see push_dst */
 
 #define LL_GEMV_PDL 1 /* launch with programmatic stream serialization (prologue overlap) */
 
@@ -126,6 +127,12 @@ typedef struct ll_gemv_args {
   void* v_cache;
   int32_t n_head, head_size, cache_len;
   int32_t grid; /* 0 = one CTA per SM; >0 forces the CTA count (tests).  CTAs own whole 16-column tiles. */
+  /* LL_EPI_PUSH (tensor parallel, row-parallel layer): the bf16 result [M][N] is stored into push_dst[r] for every
+   * rank r < push_world (peer-mapped receive buffers, the local one included; y is not used), then every CTA adds 1 to
+   * *push_cnt[r] with release semantics at system scope: compute and the first half of the all-reduce in one kernel. */
+  uint64_t push_dst[8];
+  uint64_t push_cnt[8];
+  int32_t push_world;
 } ll_gemv_args;
 
 /* Host query: LL_OK if the GEMV takes (N, K, group, nmat, M) (LL_ERR_UNSUPPORTED otherwise, e.g. M*K too
@@ -189,6 +196,11 @@ LL_API int ll_sample_topk(const void* logits, int V, float temperature, int top_
  * ------------------------------------------------------------------------------------- */
 LL_API int ll_tp_allreduce_add(void* x, const uint64_t* peer_parts, const uint64_t* peer_flags, int32_t* epoch_counter, int rank,
                         int world, int n, ll_stream stream);
+/* Second half of the pushed exchange (LL_EPI_PUSH): wait until `arrivals` more CTAs have signalled the counter of the
+ * current buffer (cnt[j], j alternating 0, 1 from call to call), then x = bf16(x + bf16(sum_r recv[j][r])) from LOCAL
+ * memory, rank order.  recv: [2][world][n] bf16 in this rank's symmetric memory; cnt: uint32[2], zero before first use. */
+LL_API int ll_tp_reduce_add(void* x, const void* recv, uint32_t* cnt, int32_t* epoch_counter, int world, int n, int arrivals,
+                     ll_stream stream);
 
 /* ---------------------------------------------------------------------------------------
  * model.py kernels

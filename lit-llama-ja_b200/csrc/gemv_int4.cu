@@ -66,6 +66,9 @@ struct Params {
   __nv_bfloat16* k_cache;
   __nv_bfloat16* v_cache;
   int n_head, head_size, cache_len;
+  __nv_bfloat16* push_dst[8];  // LL_EPI_PUSH: every rank's receive buffer for this rank's partial sums
+  uint32_t* push_cnt[8];       //              and its arrival counter
+  int push_world;
   // shared-memory plan
   int S;          // ring slots
   int xs_stride;  // bytes per staged x row
@@ -481,7 +484,15 @@ __global__ void __launch_bounds__((W + 1) * 32, 2) gemv_int4_kernel(const __grid
       vals[e] = v;
     }
     __syncwarp();
-    if (p.epilogue == LL_EPI_STORE) {
+    if (p.epilogue == LL_EPI_PUSH) {
+      // row-parallel layer under tensor parallelism: this rank's partial sums go straight into every rank's
+      // receive buffer over NVLink (fire-and-forget stores; the arrival is signalled once per CTA below)
+      for (int e = lane; e < MT; e += 32) {
+        const int m = e >> 4, n = n0 + (e & 15);
+        const __nv_bfloat16 v = __float2bfloat16_rn(vals[e]);
+        for (int r = 0; r < p.push_world; ++r) p.push_dst[r][(size_t)m * p.N + n] = v;
+      }
+    } else if (p.epilogue == LL_EPI_STORE) {
       const float bias = pre[0];
       for (int e = lane; e < MT; e += 32) {
         const int m = e >> 4, n = n0 + (e & 15);
@@ -529,6 +540,15 @@ __global__ void __launch_bounds__((W + 1) * 32, 2) gemv_int4_kernel(const __grid
       }
     }
     __syncwarp();
+  }
+  if (p.epilogue == LL_EPI_PUSH) {
+    // all of this CTA's peer stores happen-before the barrier; one thread per rank then publishes them: the
+    // release at system scope is cumulative over what the barrier made visible to that thread
+    consumer_sync(NCONS);
+    if (ctid < p.push_world) {
+      asm volatile("fence.acq_rel.sys;" ::: "memory");
+      asm volatile("red.release.sys.global.add.u32 [%0], 1;" ::"l"(p.push_cnt[ctid]) : "memory");
+    }
   }
   TRACE(6);
 }
@@ -750,10 +770,14 @@ int ll_int4_gemv_plan(int N, int K, int group, int nmat, int M, int grid, size_t
 
 int ll_int4_gemv(const ll_gemv_args* a, ll_stream stream) {
   LL_CHECK_ARG(a != nullptr, "null args");
-  LL_CHECK_ARG(a->w && a->x && a->y, "null pointer in gemv args");
   LL_CHECK_ARG(a->M >= 1 && a->M <= MAXM, "M must be in 1..8 (got %d)", a->M);
   LL_CHECK_ARG(a->N > 0 && a->K > 0 && a->group > 0, "bad shape N=%d K=%d group=%d", a->N, a->K, a->group);
-  LL_CHECK_ARG(a->epilogue >= 0 && a->epilogue <= 3, "bad epilogue %d", a->epilogue);
+  LL_CHECK_ARG(a->epilogue >= 0 && a->epilogue <= 4, "bad epilogue %d", a->epilogue);
+  LL_CHECK_ARG(a->w && a->x && (a->y || a->epilogue == LL_EPI_PUSH), "null pointer in gemv args");
+  if (a->epilogue == LL_EPI_PUSH) {
+    LL_CHECK_ARG(a->push_world >= 1 && a->push_world <= 8, "LL_EPI_PUSH: push_world must be 1..8");
+    for (int r = 0; r < a->push_world; ++r) LL_CHECK_ARG(a->push_dst[r] && a->push_cnt[r], "LL_EPI_PUSH: null destination for rank %d", r);
+  }
   const int nmat = a->epilogue == LL_EPI_SWIGLU ? 2 : 1;
   if (nmat == 2) LL_CHECK_ARG(a->w2 != nullptr, "SWIGLU epilogue needs w2");
   LL_CHECK_ARG(((uintptr_t)a->w & 15) == 0 && ((uintptr_t)a->w2 & 15) == 0 && ((uintptr_t)a->x & 15) == 0,
@@ -783,6 +807,13 @@ int ll_int4_gemv(const ll_gemv_args* a, ll_stream stream) {
   p.rope = a->rope; p.pos = a->pos;
   p.k_cache = (__nv_bfloat16*)a->k_cache; p.v_cache = (__nv_bfloat16*)a->v_cache;
   p.n_head = a->n_head; p.head_size = a->head_size; p.cache_len = a->cache_len;
+  if (a->epilogue == LL_EPI_PUSH) {
+    p.push_world = a->push_world;
+    for (int r = 0; r < a->push_world; ++r) {
+      p.push_dst[r] = (__nv_bfloat16*)(uintptr_t)a->push_dst[r];
+      p.push_cnt[r] = (uint32_t*)(uintptr_t)a->push_cnt[r];
+    }
+  }
   
   p.S = pl.S; p.xs_stride = pl.xs_stride; p.ts_max = pl.ts_max;
   p.off_xs = pl.off_xs; p.off_sx = pl.off_sx; p.off_red = pl.off_red;

@@ -38,6 +38,9 @@ __global__ void __launch_bounds__(1024) tp_allreduce_add_kernel(const __grid_con
                                                                 int32_t* __restrict__ epoch_counter, int rank, int world, int n) {
   __shared__ int s_epoch;
   if (threadIdx.x == 0) s_epoch = ++(*epoch_counter);  // same call count on every rank -> same epoch
+  // (A plain launch on purpose.  Measured on 2 GPUs, 65B: launching this kernel with the programmatic attribute and
+  // triggering the next GEMV early cost 8.70 -> 9.31 ms per token, like every other early launch behind a small
+  // kernel in this chain - profiles/r01_step_probe.md.)
   // the local residual vector does not depend on the peers: fetched while the flags travel
   uint4 x_first = make_uint4(0u, 0u, 0u, 0u);
   if (threadIdx.x * 8 < n) x_first = *reinterpret_cast<const uint4*>(x + threadIdx.x * 8);
@@ -86,6 +89,63 @@ __global__ void __launch_bounds__(1024) tp_allreduce_add_kernel(const __grid_con
   }
 }
 
+// Second half of the PUSHED exchange: the row-parallel GEMV's epilogue (LL_EPI_PUSH, gemv_int4.cu) has already stored
+// every rank's partial sums into every rank's receive buffer and counted its CTAs into cnt[j]; here one CTA waits for
+// the expected number of arrivals and reduces from LOCAL memory - no flag round trip and no NVLink load in this
+// kernel.  Buffers and counters alternate (j = call parity): arrivals of the next exchange from a fast peer land in the
+// other counter and cannot be mistaken for this one's.
+__global__ void __launch_bounds__(1024) tp_reduce_add_kernel(__nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ recv,
+                                                             uint32_t* __restrict__ cnt, int32_t* __restrict__ epoch_counter, int world,
+                                                             int n, int arrivals) {
+  __shared__ int s_epoch;
+  if (threadIdx.x == 0) s_epoch = ++(*epoch_counter);
+  __syncthreads();
+  const int epoch = s_epoch, j = (epoch - 1) & 1;
+  const uint32_t target = (uint32_t)((epoch + 1 - j) >> 1) * (uint32_t)arrivals;  // exchanges on buffer j so far
+  if (threadIdx.x == 0) {
+    const uint32_t* c = cnt + j;
+    uint32_t v;
+    do {
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(c) : "memory");
+    } while ((int32_t)(v - target) < 0);
+  }
+  __syncthreads();
+  uint4 x_first = make_uint4(0u, 0u, 0u, 0u);
+  if (threadIdx.x * 8 < n) x_first = *reinterpret_cast<const uint4*>(x + threadIdx.x * 8);
+  const __nv_bfloat16* base = recv + (size_t)j * world * n;
+  for (int i = threadIdx.x * 8; i < n; i += blockDim.x * 8) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int r0 = 0; r0 < world; r0 += 8) {
+      uint4 v[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {  // L1 is not coherent with the peers' stores: system-scope loads (L2)
+        v[q] = make_uint4(0u, 0u, 0u, 0u);
+        if (r0 + q < world) v[q] = ld_relaxed_sys_v4(base + (size_t)(r0 + q) * n + i);
+      }
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const uint32_t w[4] = {v[q].x, v[q].y, v[q].z, v[q].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          acc[2 * e] += bf16_bits_to_f32(w[e] & 0xffffu);
+          acc[2 * e + 1] += bf16_bits_to_f32(w[e] >> 16);
+        }
+      }
+    }
+    const uint4 xv = i == threadIdx.x * 8 ? x_first : *reinterpret_cast<const uint4*>(x + i);
+    const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float h0 = bf16r(acc[2 * e]), h1 = bf16r(acc[2 * e + 1]);
+      const uint32_t lo = f32_to_bf16_bits(__fadd_rn(bf16_bits_to_f32(xw[e] & 0xffffu), h0));
+      const uint32_t hi = f32_to_bf16_bits(__fadd_rn(bf16_bits_to_f32(xw[e] >> 16), h1));
+      o[e] = lo | (hi << 16);
+    }
+    *reinterpret_cast<uint4*>(x + i) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
 }  // namespace
 }  // namespace llb
 
@@ -112,6 +172,22 @@ int ll_tp_allreduce_add(void* x, const uint64_t* peer_parts /* host: world point
   }
   tp_allreduce_add_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(a, (__nv_bfloat16*)x, epoch_counter, rank, world, n);
   LL_LAUNCH_OK("tp_allreduce_add_kernel");
+  return LL_OK;
+}
+
+int ll_tp_reduce_add(void* x, const void* recv, uint32_t* cnt, int32_t* epoch_counter, int world, int n, int arrivals,
+                     ll_stream stream) {
+  LL_CHECK_ARG(x && recv && cnt && epoch_counter, "null pointer");
+  LL_CHECK_ARG(world >= 1 && world <= MAX_WORLD && arrivals > 0, "bad world / arrivals (%d / %d)", world, arrivals);
+  LL_CHECK_ARG(n > 0 && n % 8 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)recv & 15) == 0, "n must be a multiple of 8, buffers 16-byte aligned");
+  static bool once = false;
+  if (!once) {
+    prefer_max_smem(tp_reduce_add_kernel);
+    once = true;
+  }
+  tp_reduce_add_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)x, (const __nv_bfloat16*)recv, cnt, epoch_counter, world, n,
+                                                            arrivals);
+  LL_LAUNCH_OK("tp_reduce_add_kernel");
   return LL_OK;
 }
 

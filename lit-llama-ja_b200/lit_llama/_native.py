@@ -20,7 +20,7 @@ if not _LIB_PATH.exists():
 lib = C.CDLL(str(_LIB_PATH))
 
 LL_F32, LL_BF16, LL_F16 = 0, 1, 2
-EPI_STORE, EPI_RESIDUAL, EPI_ROPE_KV, EPI_SWIGLU = 0, 1, 2, 3
+EPI_STORE, EPI_RESIDUAL, EPI_ROPE_KV, EPI_SWIGLU, EPI_PUSH = 0, 1, 2, 3, 4
 GEMV_PDL = 1
 
 _DT = {torch.float32: LL_F32, torch.bfloat16: LL_BF16, torch.float16: LL_F16}
@@ -39,6 +39,7 @@ class GemvArgs(C.Structure):
         ("rope", vp), ("pos", vp), ("k_cache", vp), ("v_cache", vp),
         ("n_head", C.c_int32), ("head_size", C.c_int32), ("cache_len", C.c_int32),
         ("grid", C.c_int32),
+        ("push_dst", C.c_uint64 * 8), ("push_cnt", C.c_uint64 * 8), ("push_world", C.c_int32),
     ]
 
 
@@ -67,6 +68,7 @@ EXPORTS = {
     "ll_int8_linear": ([vp, i32, vp, vp, vp, vp, i32, i32, i32, C.c_float, vp, sz_t, vp], C.c_int),
     "ll_gptq_block": ([vp, i32, vp, i32, vp, vp, i32, vp, i32, vp, vp, i32, i32, i32, i32, i32, vp], C.c_int),
     "ll_sample_topk": ([vp, i32, C.c_float, i32, vp, vp, vp, vp, vp, vp], C.c_int),
+    "ll_tp_reduce_add": ([vp, vp, vp, vp, i32, i32, i32, vp], C.c_int),
     "ll_tp_allreduce_add": ([vp, vp, vp, vp, i32, i32, i32, vp], C.c_int),
     "ll_rmsnorm": ([vp, vp, vp, i32, i32, i32, C.c_float, vp], C.c_int),
     "ll_embed_ssq": ([vp, vp, vp, vp, i32, i32, vp], C.c_int),
@@ -81,7 +83,7 @@ EXPORTS = {
 }
 _fn = {name: _proto(name, a, r) for name, (a, r) in EXPORTS.items()}
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 if _fn["ll_abi_version"]() != ABI_VERSION:
     raise ImportError("libllb200.so ABI version mismatch; rebuild with lit-llama-ja_b200/build.py")
 

@@ -132,7 +132,7 @@ class DecodeEngine:
         if lin2 is not None:
             a.w2 = lin2._stream.data_ptr()
         a.N, a.K, a.group, a.M = lin.out_features, lin.in_features, lin.tile_cols, self.B
-        a.x, a.y = x.data_ptr(), y.data_ptr()
+        a.x, a.y = x.data_ptr(), (y.data_ptr() if y is not None else 0)
         if norm is not None:
             a.norm_weight, a.eps = norm.scale.data_ptr(), norm.eps
         a.epilogue, a.flags, a.grid = epi, (N.GEMV_PDL if self.use_pdl else 0), 0
@@ -151,10 +151,21 @@ class DecodeEngine:
             a_attn.n_head, a_attn.head_size, a_attn.cache_len = self.nh, cfg.head_size, self.S
             # tensor parallel: the row-parallel GEMVs store their partial sums; all-reduce, then the residual add
             # (the two exchanges of a block use alternating partial-sum buffers, see csrc/tp_allreduce.cu)
-            epi = N.EPI_STORE if self.tp else N.EPI_RESIDUAL
-            a_proj = self._gemv_args(_unwrap(blk.attn.c_proj)[0], self.att, self.parts[0] if self.tp else self.x, epi, "proj")
+            if not self.tp:
+                outs, epi = (self.x, self.x), N.EPI_RESIDUAL
+            elif self.exchange == "push":
+                outs, epi = (None, None), N.EPI_PUSH
+            else:
+                outs, epi = self.parts, N.EPI_STORE
+            a_proj = self._gemv_args(_unwrap(blk.attn.c_proj)[0], self.att, outs[0], epi, "proj")
             a_fc = self._gemv_args(blk.mlp.c_fc1, self.x, self.h, N.EPI_SWIGLU, "fc", norm=blk.rms_2, lin2=blk.mlp.c_fc2)
-            a_down = self._gemv_args(_unwrap(blk.mlp.c_proj)[0], self.h, self.parts[1] if self.tp else self.x, epi, "down")
+            a_down = self._gemv_args(_unwrap(blk.mlp.c_proj)[0], self.h, outs[1], epi, "down")
+            if epi == N.EPI_PUSH:
+                for j, a in enumerate((a_proj, a_down)):
+                    a.push_world = self.world
+                    for r in range(self.world):
+                        a.push_dst[r], a.push_cnt[r] = self._push_dst[j][r], self._push_cnt[j][r]
+                    self._arrivals[j] = self.world * N.gemv_plan(a.N, a.K, a.group, 1, self.B)[1]
             self.layers.append((a_attn, kc, vc, a_proj, a_fc, a_down))
         self.a_head = self._gemv_args(m.lm_head, self.x, self.logits, N.EPI_STORE, "head", norm=m.transformer.ln_f)
 
@@ -178,20 +189,44 @@ class DecodeEngine:
             N.gemv(a_down)
             if self.tp:
                 self._reduce_add(1)
-            n += 5 + ((2 if self.exchange == "peer" else 4) if self.tp else 0)
+            n += 5 + ((4 if self.exchange == "nccl" else 2) if self.tp else 0)
         N.gemv(self.a_head)
         self.n_launches = n + 1
 
     def _setup_exchange(self, dev):
-        """Partial-sum buffers for the row-parallel GEMVs.  "peer" (default): two symmetric-memory buffers + a flag
-        array mapped into every rank, read by csrc/tp_allreduce.cu straight over NVLink - one small kernel per
-        exchange, capturable in the step graph.  "nccl": dist.all_reduce + ll_add, run eagerly (a captured NCCL
+        """Exchange after the row-parallel GEMVs.  "peer" (default): two symmetric-memory buffers + a flag array
+        mapped into every rank, pulled by csrc/tp_allreduce.cu straight over NVLink - one small kernel per exchange.
+        "push": the GEMV epilogue stores its partial sums into every rank's symmetric-memory receive buffer and
+        signals arrival; a small kernel reduces from local memory (compute and the first half of the collective in
+        one kernel; correct, but measured 4 % slower at 65B TP2: the system-scope release at the end of every GEMV
+        CTA costs more than the pull it saves).  Both sit inside the step graph.  "nccl": dist.all_reduce + ll_add, run eagerly (a captured NCCL
         collective next to programmatic-launch kernels stalled on the 2-GPU box, profiles/r01_tp.md)."""
         import os
         B, E = self.x.shape
         rank, world, group = self.model._tp
         self.rank, self.world = rank, world
         mode = os.environ.get("LLB200_TP_EXCHANGE", "peer")
+        if mode == "push":
+            # the row-parallel GEMV's epilogue stores its partial sums into every rank's receive buffer and counts
+            # its CTAs in; ll_tp_reduce_add then sums from local memory (csrc/gemv_int4.cu LL_EPI_PUSH, tp_allreduce.cu)
+            import torch.distributed._symmetric_memory as symm
+            grp = group if group is not None else dist.group.WORLD
+            recv = symm.empty((2, world, B, E), dtype=torch.bfloat16, device=dev)
+            cnt = symm.empty((64,), dtype=torch.int32, device=dev)
+            recv.zero_()
+            cnt.zero_()
+            hb, hc = symm.rendezvous(recv, grp), symm.rendezvous(cnt, grp)
+            torch.cuda.synchronize()
+            dist.barrier(group=group)
+            slot = B * E * 2
+            self._push_dst = [[int(p) + (j * world + rank) * slot for p in hb.buffer_ptrs] for j in range(2)]
+            self._push_cnt = [[int(p) + 4 * j for p in hc.buffer_ptrs] for j in range(2)]
+            self._arrivals = [0, 0]
+            self._symm = (recv, cnt, hb, hc)
+            self.recv, self.cnt = recv, cnt
+            self.epoch = torch.zeros(1, dtype=torch.int32, device=dev)
+            self.exchange = "push"
+            return
         if mode == "peer":
             import torch.distributed._symmetric_memory as symm
             grp = group if group is not None else dist.group.WORLD
@@ -215,11 +250,14 @@ class DecodeEngine:
             self.exchange = "nccl"
             self.use_graph = False
         else:
-            raise ValueError(f"LLB200_TP_EXCHANGE must be 'peer' or 'nccl', not {mode!r}")
+            raise ValueError(f"LLB200_TP_EXCHANGE must be 'push', 'peer' or 'nccl', not {mode!r}")
 
     def _reduce_add(self, j: int):
         """x += sum over ranks of the partial result in buffer ``j``: the path's only exchange step."""
-        if self.exchange == "peer":
+        if self.exchange == "push":
+            N.call("ll_tp_reduce_add", N.ptr(self.x), N.ptr(self.recv), N.ptr(self.cnt), N.ptr(self.epoch), self.world,
+                   self.x.numel(), self._arrivals[j], N.stream())
+        elif self.exchange == "peer":
             import ctypes as C
             N.call("ll_tp_allreduce_add", N.ptr(self.x), C.cast(self._peer_parts[j], C.c_void_p), C.cast(self._peer_flags, C.c_void_p),
                    N.ptr(self.epoch), self.rank, self.world, self.x.numel(), N.stream())

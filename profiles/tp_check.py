@@ -1,5 +1,5 @@
 """Multi-GPU tensor-parallel check (torchrun, see run_tp.sh): prints progress lines so a stall can be located.
-  python -m torch.distributed.run ... profiles/tp_check.py [peer|nccl]
+  python -m torch.distributed.run ... profiles/tp_check.py [push|peer|nccl]
 1. the peer-memory all-reduce kernel alone against a host sum;  2. module path and fused engine on the tiny golden
 model against the single-GPU result;  3. logits identical on every rank and from run to run."""
 import os
