@@ -55,5 +55,35 @@ def build(force=False, verbose=False):
     return OUT
 
 
+def build_variant(name, defines, verbose=False):
+    """Tuning build: the same sources with extra -D flags -> lit_llama/libllb200_<name>.so (select it at run time
+    with LLB200_LIB=<path>; the default library is untouched)."""
+    objdir = CSRC / f"_obj_{name}"
+    objdir.mkdir(exist_ok=True)
+    out = HERE / "lit_llama" / f"libllb200_{name}.so"
+    procs = []
+    for src in sources():
+        obj = objdir / (src.stem + ".o")
+        cmd = [NVCC, *FLAGS, *[f"-D{d}" for d in defines], "-c", str(src), "-o", str(obj)]
+        procs.append((src, obj, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    objs, log = [], []
+    for src, obj, p in procs:
+        o, _ = p.communicate()
+        log.append(f"== {src.name}\n{o}")
+        if p.returncode != 0:
+            sys.stderr.write("\n".join(log))
+            raise RuntimeError(f"nvcc failed on {src.name}")
+        objs.append(str(obj))
+    subprocess.run([NVCC, "-shared", "-o", str(out), *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-lcudart"], check=True)
+    (objdir / "build.log").write_text("\n".join(log))
+    if verbose:
+        print("\n".join(log))
+    return out
+
+
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--variant" in sys.argv:  # python build.py --variant xpred LLB_XPRED=1 [...]
+        i = sys.argv.index("--variant")
+        print(build_variant(sys.argv[i + 1], [a for a in sys.argv[i + 2:] if not a.startswith("-")], verbose="-v" in sys.argv))
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

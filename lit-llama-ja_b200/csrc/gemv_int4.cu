@@ -100,6 +100,12 @@ __device__ __forceinline__ uint32_t rotr(uint32_t a, uint32_t n) {
   asm("shf.r.wrap.b32 %0, %1, %1, %2;" : "=r"(r) : "r"(a), "r"(n));
   return r;
 }
+template <int S>
+__device__ __forceinline__ uint32_t shr_fma(uint32_t a) {  // a >> S, issued to the FMA pipe
+  uint32_t r;
+  asm("mul.hi.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "n"(1u << (32 - S)));
+  return r;
+}
 // 1-D bulk copy global -> shared with an L2 cache policy, completion on an mbarrier.
 __device__ __forceinline__ void bulk_load_1d_hint(void* dst, const void* src, uint32_t bytes, uint64_t* bar,
                                                   uint64_t policy) {
@@ -140,8 +146,10 @@ __device__ __forceinline__ int32_t ld_acquire_gpu(const int32_t* p) {
   return v;
 }
 
+// W <= 8: two CTAs per SM (this GEMV and the next one co-reside under programmatic dependent launch, <= 112
+// registers).  W >= 12 (tuning configurations): one CTA per SM with the whole shared memory as the ring.
 template <int W, int KSP, int BPW>
-__global__ void __launch_bounds__((W + 1) * 32, 2) gemv_int4_kernel(const __grid_constant__ Params p) {
+__global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_kernel(const __grid_constant__ Params p) {
   constexpr int KB = 32 * KSP;
   constexpr int BLK = KB * 8 + TAIL_BYTES;
   constexpr int CH = W * BPW;  // items per chunk: BPW consecutive blocks per consumer warp
@@ -359,6 +367,16 @@ __global__ void __launch_bounds__((W + 1) * 32, 2) gemv_int4_kernel(const __grid
   float out[4] = {0.f, 0.f, 0.f, 0.f};
   int cur_vt = -1;
   const uint32_t xs_lane = smem_u32(xs) + (uint32_t)(min(g, M) * p.xs_stride + tig * 16);  // rows >= M read zeros
+#if defined(LLB_ABL_NO_XLD)  // timing ablation (wrong sums): no B-fragment loads
+#define LLB_XLD(addr) make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u)
+#elif defined(LLB_XPRED)
+  // only the lanes holding a real batch row fetch their B fragment (for M = 1 that is one quarter-warp: one
+  // shared-memory wavefront per LDS.128 instead of four); the others keep zeros in registers
+  const bool xl = g < M;
+#define LLB_XLD(addr) (xl ? lds128(addr) : make_uint4(0u, 0u, 0u, 0u))
+#else
+#define LLB_XLD(addr) lds128(addr)
+#endif
   const uint32_t sx_lane = smem_u32(sx) + (uint32_t)(tig * 8);
   const uint32_t ring_u = smem_u32(ring) + (uint32_t)(warp * BPW * BLK);
   const uint32_t full_u = smem_u32(full), empty_u = smem_u32(empty);
@@ -376,11 +394,27 @@ __global__ void __launch_bounds__((W + 1) * 32, 2) gemv_int4_kernel(const __grid
     }
   };
   auto mma_word = [&](float (&a)[4], uint32_t w, uint32_t b0, uint32_t b1) {
+#if defined(LLB_ABL_NO_DEQ)  // timing ablation (wrong sums): no de-quantisation arithmetic
+    mma_bf16_16816(a, w, w, w, w, b0, b1);
+#else
     const uint32_t a0 = lop_and_or(w, NIB_MASK, NIB_MAGIC);
+#ifdef LLB_SHIFT_FMA
+    // the two plain right shifts as IMAD.HI (w * 2^(32-s) >> 32) on the FMA pipe.  Measured SLOWER on B200
+    // (qpfd 1426 -> 1596 us per 32 layers: IMAD.HI is not a half-rate instruction); kept as a tuning switch.
+    const uint32_t a1 = lop_and_or(shr_fma<4>(w), NIB_MASK, NIB_MAGIC);
+    const uint32_t a2 = lop_and_or(shr_fma<8>(w), NIB_MASK, NIB_MAGIC);
+#else
     const uint32_t a1 = lop_and_or(w >> 4, NIB_MASK, NIB_MAGIC);
     const uint32_t a2 = lop_and_or(w >> 8, NIB_MASK, NIB_MAGIC);
+#endif
     const uint32_t a3 = lop_and_or(rotr(w, 12), NIB_MASK, NIB_MAGIC);
+#if defined(LLB_ABL_NO_MMA)  // timing ablation (wrong sums): de-quantise, no tensor-core instruction
+    asm volatile("" ::"r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+    a[0] += 1.f;
+#else
     mma_bf16_16816(a, a0, a1, a2, a3, b0, b1);
+#endif
+#endif
   };
 
   int it = i0 + warp * BPW;  // first item of this warp in the current chunk
@@ -388,19 +422,25 @@ __global__ void __launch_bounds__((W + 1) * 32, 2) gemv_int4_kernel(const __grid
   int slot = 0;
   uint32_t phase = 0;
   for (int ch = 0; ch < nch; ++ch) {
+    // The BPW blocks a warp takes from a chunk share their (tile, matrix) and lie inside the CTA's range together
+    // (the host guarantees G % BPW == 0).  So the tile-change test is ONE warp-uniform test per chunk, ahead of the
+    // loads: the body below is straight-line code in which the fold of one block overlaps the MMAs of the next.
+    // (Measured: a per-block test between the MMAs and the fold cost a third of the kernel's time.)
+    const bool valid = it < i1;
+    if (valid && vt != cur_vt) {
+      if (cur_vt >= 0) flush(cur_vt);
+      cur_vt = vt;
+      out[0] = out[1] = out[2] = out[3] = 0.f;
+    }
     mbar_wait_u32(full_u + slot * 8, phase);
-    const uint32_t blk0 = ring_u + (uint32_t)(slot * CHB);
-    float t[BPW][4];
-    uint2 sz[BPW], sxv[BPW];
-    int bvt[BPW];
-    {
-      int v2 = vt, g2 = gk;
+    if (valid) {
+      const uint32_t blk0 = ring_u + (uint32_t)(slot * CHB);
+      float t[BPW][4];
+      uint2 sz[BPW], sxv[BPW];
 #pragma unroll
       for (int b = 0; b < BPW; ++b) {
-        bvt[b] = (it + b < i1) ? v2 : -1;
-        // blocks past the end of the range read stale ring bytes: harmless, their sums are dropped
         const uint32_t blk = blk0 + b * BLK;
-        const int gg = (it + b < i1) ? g2 : 0;
+        const int gg = gk + b;
         sz[b] = lds64(blk + KB * 8 + g * 8);
         sxv[b] = lds64(sx_lane + gg * 32);
         const uint32_t xk = xs_lane + (uint32_t)(gg * KB * 2);
@@ -409,15 +449,15 @@ __global__ void __launch_bounds__((W + 1) * 32, 2) gemv_int4_kernel(const __grid
         for (int i = 0; i < 4; ++i) acc[0][i] = acc[1][i] = acc[2][i] = acc[3][i] = 0.f;
         if constexpr (KSP == 1) {
           const uint2 wq = lds64(blk + lane * 8);
-          const uint4 xv = lds128(xk);
+          const uint4 xv = LLB_XLD(xk);
           mma_word(acc[0], wq.x, xv.x, xv.y);
           mma_word(acc[1], wq.y, xv.z, xv.w);
         } else {
 #pragma unroll
           for (int h = 0; h < KSP / 2; ++h) {
             const uint4 wq = lds128(blk + h * 512 + lane * 16);
-            const uint4 xa = lds128(xk + (2 * h) * 64);
-            const uint4 xb = lds128(xk + (2 * h + 1) * 64);
+            const uint4 xa = LLB_XLD(xk + (2 * h) * 64);
+            const uint4 xb = LLB_XLD(xk + (2 * h + 1) * 64);
             mma_word(acc[0], wq.x, xa.x, xa.y);
             mma_word(acc[1], wq.y, xa.z, xa.w);
             mma_word(acc[2], wq.z, xb.x, xb.y);
@@ -426,20 +466,11 @@ __global__ void __launch_bounds__((W + 1) * 32, 2) gemv_int4_kernel(const __grid
         }
 #pragma unroll
         for (int i = 0; i < 4; ++i) t[b][i] = (acc[0][i] + acc[1][i]) + (acc[2][i] + acc[3][i]);
-        if (++g2 == G) {
-          g2 = 0;
-          ++v2;
-        }
       }
-    }
+      // the folds come after all of the chunk's MMAs (measured: folding block b behind block b+1's MMAs and
+      // handing the slot back before the last fold is 7 % slower, profiles/r01_gemv_experiments.md)
 #pragma unroll
-    for (int b = 0; b < BPW; ++b) {
-      if (bvt[b] >= 0) {
-        if (bvt[b] != cur_vt) {
-          if (cur_vt >= 0) flush(cur_vt);
-          cur_vt = bvt[b];
-          out[0] = out[1] = out[2] = out[3] = 0.f;
-        }
+      for (int b = 0; b < BPW; ++b) {
         const float s0 = __uint_as_float(sz[b].x << 16), zn0 = __uint_as_float(sz[b].x & 0xffff0000u);
         const float s1 = __uint_as_float(sz[b].y << 16), zn1 = __uint_as_float(sz[b].y & 0xffff0000u);
         const float sx0 = __uint_as_float(sxv[b].x), sx1 = __uint_as_float(sxv[b].y);
@@ -654,6 +685,7 @@ int make_plan(int N, int K, int group, int nmat, int M, int grid, bool has_norm,
   Plan& q = *pl;
   q.KB = KB; q.KSP = KB / 32; q.BLK = block_bytes(KB);
   consumer_config(M, q.KSP, &q.W, &q.BPW);
+  while ((K / KB) % q.BPW != 0) q.BPW >>= 1;  // the blocks a warp takes from one chunk must share their tile (kernel main loop)
   q.G = K / KB; q.GT = nmat * q.G; q.ntiles = N / TILE_N;
   const long long items = (long long)q.ntiles * q.GT;
   if (items > 0x3fffffff) {
@@ -679,7 +711,7 @@ int make_plan(int N, int K, int group, int nmat, int M, int grid, bool has_norm,
   const int ch = q.W * q.BPW;
   const size_t chb = (size_t)ch * q.BLK;
   const int nch_max = (ipc_max + ch - 1) / ch;
-  long s = ((long)SMEM_CORESIDENT - (long)fixed) / (long)chb;
+  long s = ((long)(q.W >= 12 ? SMEM_SOLO : SMEM_CORESIDENT) - (long)fixed) / (long)chb;
   if (s < 3 && nch_max > s) s = ((long)SMEM_SOLO - (long)fixed) / (long)chb;
   if (s > MAX_SLOTS) s = MAX_SLOTS;
   if (s > nch_max) s = nch_max;

@@ -11,7 +11,10 @@ from pathlib import Path
 
 import torch
 
-_LIB_PATH = Path(__file__).resolve().parent / "libllb200.so"
+import os
+
+# LLB200_LIB: a tuning build of the same library (build.py --variant); the default is the in-tree libllb200.so
+_LIB_PATH = Path(os.environ.get("LLB200_LIB") or Path(__file__).resolve().parent / "libllb200.so")
 if not _LIB_PATH.exists():
     raise ImportError(
         f"{_LIB_PATH} not found: the CUDA kernels are not built. Run `python lit-llama-ja_b200/build.py` "
