@@ -129,6 +129,9 @@ template <> struct vec_ld<float> {
   }
 };
 
+// Registers: 151 at the natural allocation.  Capping the kernel at 128 (so that two CTAs fit an SM next to a GEMV
+// CTA) costs 10 % of its time and does not remove the penalty of overlapping it with the neighbouring GEMVs
+// (profiles/r01_gemv_experiments.md).
 // CL: the splits of one (batch, head) form a thread-block cluster (nsplit <= 8) and hand their partial states to the
 // cluster's first CTA through distributed shared memory - no global scratch, fence, atomic or reload on the way.
 template <typename T, int HS, bool CL>
@@ -143,10 +146,13 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
   __shared__ float s_o[NW * 4][HS];
   __shared__ float c_st[CL ? 8 : 1][HS + 2];  // leader CTA: (M, L, O[HS]) of every split
   __shared__ int s_last;
-  if (use_pdl) {
-    pdl_launch_dependents();
-    pdl_wait();
-  }
+  // use_pdl bit 0: launched as a programmatic dependent (wait for the producer of q / the caches);
+  // bits 1-2: where this kernel lets the NEXT kernel of the stream (the c_proj GEMV: its weights do not depend on
+  // this kernel) start its prologue and ring fill: 0 = at completion, 1 = at the start, 2 = once this CTA's K/V rows
+  // have been consumed (the next kernel's weight stream then does not compete with the latency-bound K/V loads)
+  const int trig = use_pdl >> 1;
+  if (trig == 1 || (use_pdl & 1)) pdl_launch_dependents();
+  if (use_pdl & 1) pdl_wait();
   const int bh = blockIdx.x, split = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, lg = lane >> 3, li = lane & 7;
   const int nvalid = min(pos[2], S);
@@ -194,6 +200,7 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
       }
     }
   }
+  if (trig == 2) pdl_launch_dependents();
   // combine the 16 (warp, lane-group) partial states of this CTA in fixed order
   if (li == 0) { s_m[warp * 4 + lg] = m; s_l[warp * 4 + lg] = l; }
 #pragma unroll
@@ -389,6 +396,13 @@ int ll_decode_attn(const void* q, const void* k_cache, const void* v_cache, cons
     const char* e = getenv("LLB200_ATTN_CLUSTER");
     use_cluster = (e && atoi(e) == 0) ? 0 : 1;
   }
+  static int trig = -1;
+  if (trig < 0) {
+    const char* e = getenv("LLB200_ATTN_TRIGGER");
+    trig = e ? atoi(e) : 0;
+    if (trig < 0 || trig > 2) trig = 0;
+  }
+  const int kflags = (pdl ? 1 : 0) | (trig << 1);
   const bool cl = use_cluster && max_splits >= 2 && max_splits <= 8;
 #define ATTN(TT, HS)                                                                                              \
   do {                                                                                                            \
@@ -409,10 +423,10 @@ int ll_decode_attn(const void* q, const void* k_cache, const void* v_cache, cons
       cfg.attrs = attr; cfg.numAttrs = pdl ? 2 : 1;                                                               \
       LL_CUDA(cudaLaunchKernelEx(&cfg, decode_attn_kernel<TT, HS, true>, (const TT*)q, (const TT*)k_cache,        \
                                  (const TT*)v_cache, pos, (TT*)y, n_head, cache_len, max_splits, scratch, counters, \
-                                 pdl ? 1 : 0));                                                                   \
+                                 kflags));                                                                   \
     } else {                                                                                                      \
       LL_CUDA(launch(decode_attn_kernel<TT, HS, false>, grid, block, 0, st, pdl, (const TT*)q, (const TT*)k_cache, \
-                     (const TT*)v_cache, pos, (TT*)y, n_head, cache_len, max_splits, scratch, counters, pdl ? 1 : 0)); \
+                     (const TT*)v_cache, pos, (TT*)y, n_head, cache_len, max_splits, scratch, counters, kflags)); \
     }                                                                                                             \
   } while (0)
   if (dtype == LL_BF16) {
