@@ -117,7 +117,8 @@ __device__ __forceinline__ void bulk_load_1d_hint(void* dst, const void* src, ui
 }
 
 // first item of CTA c when I items are split over P CTAs; owner(x) = the CTA holding item x
-__device__ __forceinline__ int range_start(int c, int I, int P) { return (int)(((long long)c * I) / P); }
+// (c * I fits 32 bits: c <= SM count, I = tiles of one layer; the host checks it)
+__device__ __forceinline__ int range_start(int c, int I, int P) { return (int)(((unsigned)c * (unsigned)I) / (unsigned)P); }
 __device__ __forceinline__ int range_owner(int x, int I, int P) {
   return (int)((((long long)(x + 1)) * P + I - 1) / I) - 1;
 }
@@ -148,8 +149,12 @@ __device__ __forceinline__ int32_t ld_acquire_gpu(const int32_t* p) {
 
 // W <= 8: two CTAs per SM (this GEMV and the next one co-reside under programmatic dependent launch, <= 112
 // registers).  W >= 12 (tuning configurations): one CTA per SM with the whole shared memory as the ring.
-template <int W, int KSP, int BPW>
+// EPI / NORM >= 0: the epilogue / the fused RMSNorm are compile-time constants (the decode chain's hot
+// configuration gets one specialised kernel per layer kind: less code to fetch cold at every launch - the kernel
+// runs its prologue and epilogue once - and no epilogue dispatch); -1: taken from the arguments.
+template <int W, int KSP, int BPW, int EPI = -1, int NORM = -1>
 __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_kernel(const __grid_constant__ Params p) {
+  const int epilogue = EPI >= 0 ? EPI : p.epilogue;
   constexpr int KB = 32 * KSP;
   constexpr int BLK = KB * 8 + TAIL_BYTES;
   constexpr int CH = W * BPW;  // items per chunk: BPW consecutive blocks per consumer warp
@@ -229,7 +234,7 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
   const int vt_first = i0 / G, vt_last = (i1 - 1) / G;
   const int nvt = vt_last - vt_first + 1;
   const int MT = M * TILE_N;  // floats per (tile, matrix) result
-  const bool has_norm = p.norm_w != nullptr;
+  const bool has_norm = NORM >= 0 ? (NORM != 0) : (p.norm_w != nullptr);
   const int vpr = p.K >> 3;
 
   // norm weights are constants: their bulk copy into shared memory starts before the previous kernel ends
@@ -253,7 +258,7 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
   pdl_wait();  // activations (x, ssq, residual, caches, scratch) come from earlier kernels
   TRACE(2);
   int rope_pos = 0, kv_slot = 0;
-  if (p.epilogue == LL_EPI_ROPE_KV) {
+  if (epilogue == LL_EPI_ROPE_KV) {
     rope_pos = p.pos[0];
     kv_slot = p.pos[1];
   }
@@ -338,15 +343,15 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
   const int T_first = vt_first / nmat, T_last = vt_last / nmat;
   auto load_pre = [&](int T, float (&pre)[4], float2 (&cs)[2]) {
     const int n0 = T * TILE_N;
-    if (p.epilogue == LL_EPI_RESIDUAL) {
+    if (epilogue == LL_EPI_RESIDUAL) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int e = lane + 32 * j;
         if (e < MT) pre[j] = __bfloat162float(p.y[(size_t)(e >> 4) * p.N + n0 + (e & 15)]);
       }
-    } else if (p.epilogue == LL_EPI_STORE && p.bias != nullptr) {
+    } else if (epilogue == LL_EPI_STORE && p.bias != nullptr) {
       pre[0] = __bfloat162float(p.bias[n0 + (lane & 15)]);
-    } else if (p.epilogue == LL_EPI_ROPE_KV) {
+    } else if (epilogue == LL_EPI_ROPE_KV) {
       const int E = p.N / 3, hs = p.head_size;
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
@@ -515,7 +520,7 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
       vals[e] = v;
     }
     __syncwarp();
-    if (p.epilogue == LL_EPI_PUSH) {
+    if (epilogue == LL_EPI_PUSH) {
       // row-parallel layer under tensor parallelism: this rank's partial sums go straight into every rank's
       // receive buffer over NVLink (fire-and-forget stores; the arrival is signalled once per CTA below)
       for (int e = lane; e < MT; e += 32) {
@@ -523,13 +528,13 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
         const __nv_bfloat16 v = __float2bfloat16_rn(vals[e]);
         for (int r = 0; r < p.push_world; ++r) p.push_dst[r][(size_t)m * p.N + n] = v;
       }
-    } else if (p.epilogue == LL_EPI_STORE) {
+    } else if (epilogue == LL_EPI_STORE) {
       const float bias = pre[0];
       for (int e = lane; e < MT; e += 32) {
         const int m = e >> 4, n = n0 + (e & 15);
         p.y[(size_t)m * p.N + n] = __float2bfloat16_rn(vals[e] + bias);
       }
-    } else if (p.epilogue == LL_EPI_RESIDUAL) {
+    } else if (epilogue == LL_EPI_RESIDUAL) {
       // x = bf16(x + bf16(h))   (ref model.py:172-173)
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -539,7 +544,7 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
           p.y[(size_t)(e >> 4) * p.N + n0 + (e & 15)] = __float2bfloat16_rn(__fadd_rn(pre[j], h));
         }
       }
-    } else if (p.epilogue == LL_EPI_ROPE_KV) {
+    } else if (epilogue == LL_EPI_ROPE_KV) {
       const int E = p.N / 3, hs = p.head_size;
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
@@ -572,7 +577,7 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
     }
     __syncwarp();
   }
-  if (p.epilogue == LL_EPI_PUSH) {
+  if (epilogue == LL_EPI_PUSH) {
     // all of this CTA's peer stores happen-before the barrier; one thread per rank then publishes them: the
     // release at system scope is cumulative over what the barrier made visible to that thread
     consumer_sync(NCONS);
@@ -695,6 +700,10 @@ int make_plan(int N, int K, int group, int nmat, int M, int grid, bool has_norm,
   q.I = (int)items;
   q.P = grid > 0 ? grid : sms;
   if (q.P > q.ntiles) q.P = q.ntiles;  // whole tiles per CTA
+  if ((long long)q.ntiles * (q.P + 1) > 0xffffffffLL) {
+    set_error("int4 GEMV: N too large (%d)", N);
+    return LL_ERR_UNSUPPORTED;
+  }
   const int tiles_max = (q.ntiles + q.P - 1) / q.P;
   const int ipc_max = tiles_max * q.GT;
   q.ts_max = tiles_max * nmat;
@@ -727,19 +736,36 @@ int make_plan(int N, int K, int group, int nmat, int M, int grid, bool has_norm,
   return LL_OK;
 }
 
-template <int W, int KSP, int BPW>
+template <int W, int KSP, int BPW, int EPI = -1, int NORM = -1>
 int launch_cfg(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
   static size_t configured = 0;
   if (pl.smem > configured) {
-    if (configured == 0) prefer_max_smem(gemv_int4_kernel<W, KSP, BPW>);
-    LL_CUDA(cudaFuncSetAttribute(gemv_int4_kernel<W, KSP, BPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+    if (configured == 0) prefer_max_smem(gemv_int4_kernel<W, KSP, BPW, EPI, NORM>);
+    LL_CUDA(cudaFuncSetAttribute(gemv_int4_kernel<W, KSP, BPW, EPI, NORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
     configured = pl.smem;
   }
-  LL_CUDA(launch(gemv_int4_kernel<W, KSP, BPW>, dim3(pl.P), dim3((W + 1) * 32), pl.smem, st, pdl, p));
+  LL_CUDA(launch(gemv_int4_kernel<W, KSP, BPW, EPI, NORM>, dim3(pl.P), dim3((W + 1) * 32), pl.smem, st, pdl, p));
   return LL_OK;
 }
 
+bool specialise_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("LLB200_GEMV_SPECIALISE");
+    on = (e && atoi(e) == 0) ? 0 : 1;
+  }
+  return on != 0;
+}
+
 int launch_plan(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
+  // the decode chain's configuration (batch <= 2, group % 128 == 0): one kernel per layer kind
+  if (pl.W == 8 && pl.KSP == 4 && pl.BPW == 2 && specialise_enabled()) {
+    const bool norm = p.norm_w != nullptr;
+#define SPEC(e, n) \
+  if (p.epilogue == e && norm == (n != 0)) return launch_cfg<8, 4, 2, e, n>(p, pl, pdl, st)
+    SPEC(LL_EPI_ROPE_KV, 1); SPEC(LL_EPI_RESIDUAL, 0); SPEC(LL_EPI_SWIGLU, 1); SPEC(LL_EPI_STORE, 1); SPEC(LL_EPI_STORE, 0);
+#undef SPEC
+  }
 #define CFG(w, k, b) \
   if (pl.W == w && pl.KSP == k && pl.BPW == b) return launch_cfg<w, k, b>(p, pl, pdl, st)
   CFG(12, 4, 1); CFG(8, 4, 2); CFG(12, 4, 2); CFG(8, 4, 1); CFG(16, 4, 1); CFG(16, 4, 2); CFG(4, 4, 1); CFG(4, 4, 2);
