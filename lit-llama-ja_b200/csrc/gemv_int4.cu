@@ -152,7 +152,8 @@ __device__ __forceinline__ int32_t ld_acquire_gpu(const int32_t* p) {
 // EPI / NORM >= 0: the epilogue / the fused RMSNorm are compile-time constants (the decode chain's hot
 // configuration gets one specialised kernel per layer kind: less code to fetch cold at every launch - the kernel
 // runs its prologue and epilogue once - and no epilogue dispatch); -1: taken from the arguments.
-template <int W, int KSP, int BPW, int EPI = -1, int NORM = -1>
+// MM > 0: the batch (rows of x) is the compile-time constant MM (batch-1 decode: every per-row loop folds away).
+template <int W, int KSP, int BPW, int EPI = -1, int NORM = -1, int MM = 0>
 __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_kernel(const __grid_constant__ Params p) {
   const int epilogue = EPI >= 0 ? EPI : p.epilogue;
   constexpr int KB = 32 * KSP;
@@ -179,7 +180,7 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
   // whole tiles per CTA: no tile is shared between CTAs, so no cross-CTA exchange on the critical path
   const int i0 = range_start(c, p.ntiles, P) * p.GT, i1 = range_start(c + 1, p.ntiles, P) * p.GT;
   const int nch = (i1 - i0 + CH - 1) / CH;
-  const int G = p.G, S = p.S, M = p.M;
+  const int G = p.G, S = p.S, M = MM > 0 ? MM : p.M;
 
   TRACE(0);
   if (threadIdx.x == 0) {
@@ -793,33 +794,37 @@ int make_plan(int N, int K, int group, int nmat, int M, int grid, bool has_norm,
   return LL_OK;
 }
 
-template <int W, int KSP, int BPW, int EPI = -1, int NORM = -1>
+template <int W, int KSP, int BPW, int EPI = -1, int NORM = -1, int MM = 0>
 int launch_cfg(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
   static size_t configured = 0;
   if (pl.smem > configured) {
-    if (configured == 0) prefer_max_smem(gemv_int4_kernel<W, KSP, BPW, EPI, NORM>);
-    LL_CUDA(cudaFuncSetAttribute(gemv_int4_kernel<W, KSP, BPW, EPI, NORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+    if (configured == 0) prefer_max_smem(gemv_int4_kernel<W, KSP, BPW, EPI, NORM, MM>);
+    LL_CUDA(cudaFuncSetAttribute(gemv_int4_kernel<W, KSP, BPW, EPI, NORM, MM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
     configured = pl.smem;
   }
-  LL_CUDA(launch(gemv_int4_kernel<W, KSP, BPW, EPI, NORM>, dim3(pl.P), dim3((W + 1) * 32), pl.smem, st, pdl, p));
+  LL_CUDA(launch(gemv_int4_kernel<W, KSP, BPW, EPI, NORM, MM>, dim3(pl.P), dim3((W + 1) * 32), pl.smem, st, pdl, p));
   return LL_OK;
 }
 
-bool specialise_enabled() {
-  static int on = -1;
-  if (on < 0) {
+// LLB200_GEMV_SPECIALISE: 0 = the generic kernel, 1 = epilogue / norm as constants, 2 (default) = and batch 1 as a constant
+int specialise_level() {
+  static int lv = -1;
+  if (lv < 0) {
     const char* e = getenv("LLB200_GEMV_SPECIALISE");
-    on = (e && atoi(e) == 0) ? 0 : 1;
+    lv = e ? atoi(e) : 2;
+    if (lv < 0 || lv > 2) lv = 2;
   }
-  return on != 0;
+  return lv;
 }
 
 int launch_plan(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
   // the decode chain's configuration (batch <= 2, group % 128 == 0): one kernel per layer kind
-  if (pl.W == 8 && pl.KSP == 4 && pl.BPW == 2 && specialise_enabled()) {
+  if (pl.W == 8 && pl.KSP == 4 && pl.BPW == 2 && specialise_level() > 0) {
     const bool norm = p.norm_w != nullptr;
-#define SPEC(e, n) \
-  if (p.epilogue == e && norm == (n != 0)) return launch_cfg<8, 4, 2, e, n>(p, pl, pdl, st)
+    const bool m1 = p.M == 1 && specialise_level() > 1;
+#define SPEC(e, n)                                                              \
+  if (p.epilogue == e && norm == (n != 0))                                      \
+    return m1 ? launch_cfg<8, 4, 2, e, n, 1>(p, pl, pdl, st) : launch_cfg<8, 4, 2, e, n>(p, pl, pdl, st)
     SPEC(LL_EPI_ROPE_KV, 1); SPEC(LL_EPI_RESIDUAL, 0); SPEC(LL_EPI_SWIGLU, 1); SPEC(LL_EPI_STORE, 1); SPEC(LL_EPI_STORE, 0);
 #undef SPEC
   }
