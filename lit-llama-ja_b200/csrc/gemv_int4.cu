@@ -83,10 +83,16 @@ __device__ __forceinline__ unsigned long long gtimer() {
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
+// stage stamps for profiles/gemv_trace.py: only in the tuning build (build.py --variant trace LLB_TRACE=1) - the
+// stamps are code every launch would have to fetch
+#ifdef LLB_TRACE
 #define TRACE(i)                                                                   \
   do {                                                                             \
     if (p.trace != nullptr && threadIdx.x == 0) p.trace[blockIdx.x * 16 + (i)] = gtimer(); \
   } while (0)
+#else
+#define TRACE(i) do { } while (0)
+#endif
 
 __device__ __forceinline__ void consumer_sync(int n) { asm volatile("bar.sync 1, %0;" ::"r"(n) : "memory"); }
 
