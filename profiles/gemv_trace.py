@@ -1,4 +1,9 @@
-"""Stage time stamps (globaltimer) of the GEMV kernels inside a captured q,p,f,d x32 chain (7B, B=1)."""
+"""Stage time stamps (globaltimer) of the GEMV kernels inside a captured q,p,f,d x32 chain (7B, B=1).
+
+Needs the tuning build with the stamps compiled in:
+    python lit-llama-ja_b200/build.py --variant trace LLB_TRACE=1
+    LLB200_LIB=$PWD/lit-llama-ja_b200/lit_llama/libllb200_trace.so python profiles/gemv_trace.py qpfd
+"""
 import ctypes as C
 import os
 import sys
