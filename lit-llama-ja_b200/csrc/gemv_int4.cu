@@ -1,4 +1,4 @@
-// int4 (GPTQ column-block) decode GEMV for sm_100a, v2: y[M<=8][N] = x[M][K] . dequant(W)^T
+// int4 (GPTQ column-block) decode GEMV for sm_100a: y[M<=8][N] = x[M][K] . dequant(W)^T
 //
 // Replaces the reference's Triton launcher (ref: lit_llama/quantization.py:282-331, which pads
 // M=1 to 256 rows and reads every packed byte twice) and its dequantise-then-F.linear fallback
@@ -11,23 +11,27 @@
 //    A fragment = 8 nibbles placed at bit offsets 3+4i so that `(w >> 4i) & 0x00780078 | 0x41804180`
 //    IS the bf16x2 register holding (16+q, 16+q')), followed by the block's 16 (scale, -(16+zero))
 //    bf16 pairs.  7 ALU instructions per 8 weights, no per-weight scale/zero arithmetic.
-//  * Work item = one block.  Items are split evenly and CONTIGUOUSLY over one CTA per SM
-//    (stream-K), so a CTA's whole share is a contiguous byte range: one producer thread streams it
-//    with 1-D bulk TMA copies (L2 evict-first) into a shared-memory ring of chunks gated by
-//    mbarriers.  Weights do not depend on the previous kernel: under programmatic dependent launch
-//    the next GEMV's CTA co-resides (<= 110 KB smem each) and fills its ring while this one computes.
-//  * Consumer warps take one block per chunk each: LDS.128 of fragment words, dequant to bf16 by
-//    LOP3/SHF, mma.sync m16n8k16 (bf16 x bf16 -> fp32) with the weights as the A operand and up to
-//    8 batch rows of x as the B columns.  Per block: acc starts at -(16+zero)*sum(x_block), ends as
-//    sum (q-zero) x, and is folded into the running column sums with one FFMA by the scale.
-//  * x is staged once per CTA in shared memory by one bulk copy per row; the optional fused RMSNorm
-//    (ref model.py:276-283 rounding steps) is computed in place from the staged row (its sum of squares
-//    included: every CTA holds the whole row), together with the per-block sums of x.
-//  * Fixed-order reduction across warps in shared memory; tiles whose k range is shared by several
-//    CTAs go through a global scratch and the LAST-arriving contributor sums them in contributor
-//    order (deterministic, self-resetting counters) and runs the fused epilogue: plain store,
-//    residual add (+ RMSNorm sum-of-squares partials for the next kernel), RoPE + KV-cache write
-//    (c_attn), or SwiGLU (c_fc1/c_fc2 as two matrices of one launch).
+//  * Work item = one block.  Whole 16-column tiles are split contiguously over one CTA per SM, so a
+//    CTA's share is one contiguous byte range per matrix and no tile is shared between CTAs: one
+//    producer thread streams the range with 1-D bulk TMA copies (L2 evict-first) into a
+//    shared-memory ring of chunks gated by mbarriers.  Weights do not depend on the previous kernel:
+//    under programmatic dependent launch the next GEMV's CTA co-resides (<= 110 KB smem each) and
+//    fills its ring while this one computes.
+//  * Consumer warps take BPW consecutive blocks per chunk each: LDS.128 of fragment words, dequant to
+//    bf16 by LOP3/SHF, mma.sync m16n8k16 (bf16 x bf16 -> fp32) with the weights as the A operand and
+//    up to 8 batch rows of x as the B columns.  Per block: sum (16+q) x, then one FFMA pair folds
+//    -(16+zero) * sum(x_block) and the scale into the running column sums.  The blocks a warp takes
+//    from one chunk share their tile, so the chunk body is straight-line code behind ONE tile test.
+//  * x is staged once per CTA in shared memory (batched ld.global.cg, one L2 round trip); the optional
+//    fused RMSNorm (ref model.py:276-283 rounding steps) is computed from the loaded row (its sum of
+//    squares included: every CTA holds the whole row), together with the per-block sums of x.
+//  * Fixed-order reduction across warps in shared memory, then the fused epilogue, one warp per tile:
+//    plain store, residual add, RoPE + KV-cache write (c_attn), SwiGLU (c_fc1/c_fc2 as two matrices
+//    of one launch), or peer stores for the tensor-parallel push.  The decode chain's configuration
+//    gets one instantiation per (epilogue, norm, batch 1): less cold code per launch.
+//  * Measurements, ablations and rejected variants: profiles/r01_gemv_experiments.md, DESIGN.md section 3.
+//    Tuning switches (-D): LLB_XPRED, LLB_SHIFT_FMA, LLB_XSTAGE_TMA, LLB_TRACE, LLB_ABL_* (timing
+//    ablations, wrong sums) - build with `build.py --variant`, select with LLB200_LIB.
 #include <stdlib.h>
 
 #include "common.cuh"
