@@ -130,3 +130,25 @@ def test_streamk_split_invariants(ntiles, G, nmat, P):
         if r[c]["back"] and t == r[c]["t_back"]:
             covered += min(hi, r[c + 1]["i1"]) - max(lo, r[c + 1]["i0"])
         assert covered == GT
+
+
+# ----------------------------------------------------------------------------- bench.py contract (reference arm, CPU)
+def test_bench_reference_arm_prints_the_contract_line():
+    """`bench.py --impl reference` runs on the host cores only and prints ONE JSON line with the keys the driver reads."""
+    import json
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    out = subprocess.run([sys.executable, str(root / "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                         capture_output=True, text=True, timeout=600, cwd=root)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [ln for ln in out.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "decode_tokens_per_sec" and d["unit"] == "tokens/s"
+    assert d["higher_is_better"] is True and d["n_gpus"] == 1 and d["value"] > 0
+    assert d["cpu_baseline"]["kind"] in ("port", "reference") and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0 and d["e2e"]["value"] == d["value"]
+    assert "workload" in d["config"]
