@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define LL_ABI_VERSION 4
+#define LL_ABI_VERSION 5
 
 #define LL_OK 0
 #define LL_ERR_ARG (-1)         /* bad shape / dtype / null pointer */
@@ -240,12 +240,14 @@ LL_API int ll_silu_mul(const void* a, const void* b, void* y, int dtype, size_t 
 /* y = dtype(a + b) : the residual adds of Block.forward, model.py:172-173 */
 LL_API int ll_add(const void* a, const void* b, void* y, int dtype, size_t n, ll_stream stream);
 /* pos[0] += 1; pos[1] = pos[0] % cache_len; pos[2] = min(pos[0] + 1, cache_len): one decode step
- * (ref: generate.py:77 input_pos advance + model.py:221-225 sliding window). */
-LL_API int ll_advance_pos(int32_t* pos, int cache_len, ll_stream stream);
+ * (ref: generate.py:77 input_pos advance + model.py:221-225 sliding window).  A position outside [0, max_pos)
+ * (max_pos = rows of the RoPE table = block_size) traps on the device: the reference's
+ * rope_cache.index_select(0, input_pos) raises there (model.py:101). */
+LL_API int ll_advance_pos(int32_t* pos, int cache_len, int max_pos, ll_stream stream);
 /* pos[0] = input_pos[0] (device int64, the caller's position tensor); pos[1], pos[2] as above.
  * Lets LLaMA.forward(idx, max_seq_length, input_pos) honour an arbitrary input_pos without a
  * host sync (ref: model.py:101-104 index_select by input_pos). */
-LL_API int ll_set_pos(int32_t* pos, const int64_t* input_pos, int cache_len, ll_stream stream);
+LL_API int ll_set_pos(int32_t* pos, const int64_t* input_pos, int cache_len, int max_pos, ll_stream stream);
 
 #ifdef __cplusplus
 }

@@ -298,8 +298,11 @@ __global__ void add_kernel(const T* __restrict__ a, const T* __restrict__ b, T* 
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) dt<T>::st(y, i, __fadd_rn(dt<T>::ld(a, i), dt<T>::ld(b, i)));
 }
-__global__ void advance_pos_kernel(int32_t* pos, int S) {
+// A position past the RoPE table (ref: model.py:101 rope_cache.index_select raises) stops the kernel: the error
+// surfaces at the next synchronisation instead of an out-of-bounds read in the c_attn epilogue.
+__global__ void advance_pos_kernel(int32_t* pos, int S, int max_pos) {
   const int p = pos[0] + 1;
+  if (p < 0 || p >= max_pos) __trap();
   pos[0] = p;
   pos[1] = p % S;
   pos[2] = min(p + 1, S);
@@ -320,7 +323,8 @@ __global__ void apply_rope_kernel(const T* __restrict__ x, const float* __restri
   dt<T>::st(y, 2 * i + 1, __fadd_rn(__fmul_rn(x1, cs.x), __fmul_rn(x0, cs.y)));
 }
 
-__global__ void set_pos_kernel(int32_t* pos, const int64_t* input_pos, int S) {
+__global__ void set_pos_kernel(int32_t* pos, const int64_t* input_pos, int S, int max_pos) {
+  if (input_pos[0] < 0 || input_pos[0] >= (int64_t)max_pos) __trap();
   const int p = (int)input_pos[0];
   pos[0] = p;
   pos[1] = p % S;
@@ -471,9 +475,9 @@ int ll_add(const void* a, const void* b, void* y, int dtype, size_t n, ll_stream
   return LL_OK;
 }
 
-int ll_advance_pos(int32_t* pos, int cache_len, ll_stream stream) {
-  LL_CHECK_ARG(pos && cache_len > 0, "bad advance_pos arguments");
-  advance_pos_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(pos, cache_len);
+int ll_advance_pos(int32_t* pos, int cache_len, int max_pos, ll_stream stream) {
+  LL_CHECK_ARG(pos && cache_len > 0 && max_pos > 0, "bad advance_pos arguments");
+  advance_pos_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(pos, cache_len, max_pos);
   LL_LAUNCH_OK("advance_pos_kernel");
   return LL_OK;
 }
@@ -492,9 +496,9 @@ int ll_apply_rope(const void* x, const float* rope, void* y, int dtype, int B, i
   return LL_OK;
 }
 
-int ll_set_pos(int32_t* pos, const int64_t* input_pos, int cache_len, ll_stream stream) {
-  LL_CHECK_ARG(pos && input_pos && cache_len > 0, "bad set_pos arguments");
-  set_pos_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(pos, input_pos, cache_len);
+int ll_set_pos(int32_t* pos, const int64_t* input_pos, int cache_len, int max_pos, ll_stream stream) {
+  LL_CHECK_ARG(pos && input_pos && cache_len > 0 && max_pos > 0, "bad set_pos arguments");
+  set_pos_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(pos, input_pos, cache_len, max_pos);
   LL_LAUNCH_OK("set_pos_kernel");
   return LL_OK;
 }

@@ -79,9 +79,6 @@ struct Params {
   int ts_max;     // (tile, matrix) slots of the cross-warp reduction
   int off_xs, off_sx, off_red, off_wv, off_bar, off_nw;
   int prefetch_delay_ns;  // producer start delay under PDL (lets the running kernel's x staging go first)
-  // neighbour stream-K (SK kernels only): per-CTA hand-over slots [P][2][MAXM * 16] and flags [P * 32] in global memory
-  float* sk_part;
-  int32_t* sk_flag;
   unsigned long long* trace;  // debug: [P][8] globaltimer stamps of this launch, or nullptr
 };
 
@@ -129,13 +126,9 @@ __device__ __forceinline__ void bulk_load_1d_hint(void* dst, const void* src, ui
       : "memory");
 }
 
-// first item of CTA c when I items are split over P CTAs; owner(x) = the CTA holding item x
+// first tile of CTA c when I tiles are split over P CTAs
 // (c * I fits 32 bits: c <= SM count, I = tiles of one layer; the host checks it)
 __device__ __forceinline__ int range_start(int c, int I, int P) { return (int)(((unsigned)c * (unsigned)I) / (unsigned)P); }
-__device__ __forceinline__ int range_owner(int x, int I, int P) {
-  return (int)((((long long)(x + 1)) * P + I - 1) / I) - 1;
-}
-
 constexpr uint32_t NIB_MASK = 0x00780078u;   // nibble at bits 3..6 of each bf16 half
 constexpr uint32_t NIB_MAGIC = 0x41804180u;  // bf16 16.0: 16 + q exact for q in 0..15
 
@@ -151,29 +144,15 @@ __device__ __forceinline__ void mbar_wait_u32(uint32_t bar, uint32_t parity) {
       "r"(parity)
       : "memory");
 }
-__device__ __forceinline__ void st_release_gpu(int32_t* p, int32_t v) {
-  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ int32_t ld_acquire_gpu(const int32_t* p) {
-  int32_t v;
-  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-
 // W <= 8: two CTAs per SM (this GEMV and the next one co-reside under programmatic dependent launch, <= 112
 // registers).  W >= 12 (tuning configurations): one CTA per SM with the whole shared memory as the ring.
 // EPI / NORM >= 0: the epilogue / the fused RMSNorm are compile-time constants (the decode chain's hot
 // configuration gets one specialised kernel per layer kind: less code to fetch cold at every launch - the kernel
 // runs its prologue and epilogue once - and no epilogue dispatch); -1: taken from the arguments.
 // MM > 0: the batch (rows of x) is the compile-time constant MM (batch-1 decode: every per-row loop folds away).
-// SK = 1 (opt-in, LLB200_GEMV_STREAMK=1; NOT yet measured): neighbour stream-K.  Items are split evenly over the CTAs, so a
-// tile may be shared by CTA c (which owns the tile's first item, needs the tile LAST and runs its epilogue) and CTA c+1
-// (which computes its part of the tile FIRST).  CTA c+1 publishes the sums of its part as soon as its warps are past
-// that tile - early in its main loop - and CTA c adds them in its epilogue: the hand-over is off the critical path of both,
-// unlike v2's last-arriver combine.  Every range holds at least one whole tile's worth of items (host), so a tile has at
-// most two contributors; the order of the sum is fixed (own warps in order, then the neighbour's part): deterministic for
-// a given grid, but no longer identical across grid sizes.
-template <int W, int KSP, int BPW, int EPI = -1, int NORM = -1, int MM = 0, int SK = 0>
+// (A neighbour stream-K split of the boundary tiles was built and measured in round 2: q 311 -> 361, p 131 -> 199, f 423 -> 519,
+// d 277 -> 325 us per 32 layers - slower than the 7-14 % tile imbalance it removes; taken out, profiles/r02_gemv_experiments.md.)
+template <int W, int KSP, int BPW, int EPI = -1, int NORM = -1, int MM = 0>
 __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_kernel(const __grid_constant__ Params p) {
   const int epilogue = EPI >= 0 ? EPI : p.epilogue;
   constexpr int KB = 32 * KSP;
@@ -198,9 +177,8 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int P = gridDim.x, c = blockIdx.x;
   // whole tiles per CTA: no tile is shared between CTAs, so no cross-CTA exchange on the critical path
-  // (SK: an even split of the items in units of BPW blocks)
-  const int i0 = SK ? range_start(c, p.I / BPW, P) * BPW : range_start(c, p.ntiles, P) * p.GT;
-  const int i1 = SK ? range_start(c + 1, p.I / BPW, P) * BPW : range_start(c + 1, p.ntiles, P) * p.GT;
+  const int i0 = range_start(c, p.ntiles, P) * p.GT;
+  const int i1 = range_start(c + 1, p.ntiles, P) * p.GT;
   const int nch = (i1 - i0 + CH - 1) / CH;
   const int G = p.G, S = p.S, M = MM > 0 ? MM : p.M;
 
@@ -255,15 +233,7 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
   const int g = lane >> 2, tig = lane & 3;
   const int ctid = threadIdx.x;  // 0..NCONS-1
   const int vt_first = i0 / G, vt_last = (i1 - 1) / G;
-  // SK: the front tile belongs to CTA c-1 if this range starts inside it; the back tile is shared with CTA c+1 if this
-  // range ends inside it.  Slots of `red` reach to the end of the back tile (the matrices this CTA does not touch stay 0).
-  const int sk_T_front = i0 / p.GT, sk_T_back = (i1 - 1) / p.GT;
-  const bool sk_front = SK && (i0 != sk_T_front * p.GT);
-  const bool sk_back = SK && (i1 != (sk_T_back + 1) * p.GT);
-  const int sk_front_end = (sk_T_front + 1) * p.GT;  // first item past the front tile
-  const int nvt = SK ? (sk_T_back + 1) * p.nmat - vt_first : vt_last - vt_first + 1;
-  __shared__ int s_sk_cnt;
-  if (SK && ctid == 0) s_sk_cnt = 0;
+  const int nvt = vt_last - vt_first + 1;
   const int MT = M * TILE_N;  // floats per (tile, matrix) result
   const bool has_norm = NORM >= 0 ? (NORM != 0) : (p.norm_w != nullptr);
   const int vpr = p.K >> 3;
@@ -428,7 +398,7 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
   // epilogue operands that do not depend on this kernel's sums (residual stream, bias, RoPE row) are
   // fetched now for this warp's first tile, behind the main loop
   const int nmat = p.nmat;
-  const int T_first = vt_first / nmat + (sk_front ? 1 : 0), T_last = vt_last / nmat;
+  const int T_first = vt_first / nmat, T_last = vt_last / nmat;
   auto load_pre = [&](int T, float (&pre)[4], float2 (&cs)[2]) {
     const int n0 = T * TILE_N;
     if (epilogue == LL_EPI_RESIDUAL) {
@@ -486,37 +456,6 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
       r[m1 * TILE_N + g + 8] = out[3];
     }
   };
-  // SK: a warp that is past the front tile says so; the last one sums the front tile's parts over the warps (same
-  // order as the epilogue) and publishes them for CTA c-1
-  bool sk_front_pending = sk_front;
-  auto sk_signal = [&]() {
-    __syncwarp();
-    int old = 0;
-    if (lane == 0) {
-      __threadfence_block();
-      old = atomicAdd(&s_sk_cnt, 1);
-    }
-    old = __shfl_sync(0xffffffffu, old, 0);
-    if (old == W - 1) {
-      __threadfence_block();
-      float* dst = p.sk_part + (size_t)c * 2 * (MAXM * TILE_N);
-      for (int vtf = vt_first; vtf < (sk_T_front + 1) * p.nmat; ++vtf) {
-        const int j = vtf - sk_T_front * p.nmat;
-        for (int e = lane; e < MT; e += 32) {
-          const float* r = red + (size_t)(vtf - vt_first) * W * MT + e;
-          float v = 0.f;
-#pragma unroll
-          for (int w = 0; w < W; ++w) v += r[w * MT];
-          dst[j * (MAXM * TILE_N) + e] = v;
-        }
-      }
-      __syncwarp();
-      if (lane == 0) {
-        __threadfence();
-        st_release_gpu(p.sk_flag + c * 32, 1);
-      }
-    }
-  };
   auto mma_word = [&](float (&a)[4], uint32_t w, uint32_t b0, uint32_t b1) {
 #if defined(LLB_ABL_NO_DEQ)  // timing ablation (wrong sums): no de-quantisation arithmetic
     mma_bf16_16816(a, w, w, w, w, b0, b1);
@@ -555,12 +494,6 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
       if (cur_vt >= 0) flush(cur_vt);
       cur_vt = vt;
       out[0] = out[1] = out[2] = out[3] = 0.f;
-    }
-    if constexpr (SK != 0) {
-      if (sk_front_pending && valid && it >= sk_front_end) {  // this warp's front-tile sums are flushed
-        sk_front_pending = false;
-        sk_signal();
-      }
     }
     mbar_wait_u32(full_u + slot * 8, phase);
     if (valid) {
@@ -625,9 +558,6 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
     }
   }
   if (cur_vt >= 0) flush(cur_vt);
-  if constexpr (SK != 0) {
-    if (sk_front_pending) sk_signal();  // a warp whose items all lay in the front tile (or that had none)
-  }
   TRACE(4);
   consumer_sync(NCONS);
 
@@ -648,22 +578,6 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
       vals[e] = v;
     }
     __syncwarp();
-    if constexpr (SK != 0) {
-      if (sk_back && T == sk_T_back) {  // CTA c+1 computed the rest of this tile first: its part has long arrived
-        if (lane == 0) {
-          while (ld_acquire_gpu(p.sk_flag + (c + 1) * 32) == 0) {
-          }
-        }
-        __syncwarp();
-        const float* src = p.sk_part + (size_t)(c + 1) * 2 * (MAXM * TILE_N);
-        for (int vtb = i1 / G; vtb < (sk_T_back + 1) * nmat; ++vtb) {
-          const int j = vtb - sk_T_back * nmat;
-          for (int e = lane; e < MT; e += 32) vals[j * MT + e] += __ldcg(src + j * (MAXM * TILE_N) + e);
-        }
-        __syncwarp();
-        if (lane == 0) p.sk_flag[(c + 1) * 32] = 0;  // for the next launch (ordered by the kernel boundary)
-      }
-    }
     if (epilogue == LL_EPI_PUSH) {
       // row-parallel layer under tensor parallelism: this rank's partial sums go straight into every rank's
       // receive buffer over NVLink (fire-and-forget stores; the arrival is signalled once per CTA below)
@@ -788,7 +702,6 @@ __global__ void int4_repack_kernel(const uint8_t* __restrict__ qw, const P* __re
 
 // ------------------------------------------------------------------------------------ host side
 struct Plan {
-  int streamk;  // neighbour stream-K split (opt-in), see the kernel
   int KB, KSP, BLK, W, BPW;
   int G, GT, ntiles, I, P;
   int ts_max, S;
@@ -800,15 +713,6 @@ unsigned long long* g_trace = nullptr;  // debug: device buffer [launches][256][
 int g_trace_launches = 0, g_trace_idx = 0;
 
 int specialise_level();
-bool streamk_requested() {
-  static int on = -1;
-  if (on < 0) {
-    const char* e = getenv("LLB200_GEMV_STREAMK");
-    on = (e && atoi(e) == 1) ? 1 : 0;
-  }
-  return on != 0;
-}
-
 constexpr int SMEM_CORESIDENT = 110 * 1024;  // two such CTAs (this GEMV + the next one, under PDL) fit one SM
 constexpr int SMEM_SOLO = 220 * 1024;
 constexpr int MAX_SLOTS = 12;
@@ -831,7 +735,7 @@ void consumer_config(int M, int KSP, int* W, int* BPW) {
 }
 
 // Fills `pl`; returns LL_OK, or LL_ERR_UNSUPPORTED with a message when the shape does not fit.
-int make_plan(int N, int K, int group, int nmat, int M, int grid, bool has_norm, Plan* pl, bool allow_sk = false) {
+int make_plan(int N, int K, int group, int nmat, int M, int grid, bool has_norm, Plan* pl) {
   const int KB = pick_kb(K, group);
   if (KB == 0 || N % TILE_N != 0 || K % 8 != 0) {
     set_error("int4 GEMV needs N %% 16 == 0, K %% group == 0 and group %% 32 == 0 (N=%d K=%d group=%d)", N, K, group);
@@ -859,14 +763,9 @@ int make_plan(int N, int K, int group, int nmat, int M, int grid, bool has_norm,
     set_error("int4 GEMV: N too large (%d)", N);
     return LL_ERR_UNSUPPORTED;
   }
-  // neighbour stream-K: opt-in, batch-1 decode configuration only, the default grid, every range >= one tile of items
-  q.streamk = 0;
-  if (allow_sk && grid <= 0 && M == 1 && q.W == 8 && q.KSP == 4 && q.BPW == 2 && q.P == sms &&
-      (q.I / q.BPW / q.P) * q.BPW >= q.GT)
-    q.streamk = 1;
   const int tiles_max = (q.ntiles + q.P - 1) / q.P;
-  const int ipc_max = q.streamk ? ((q.I / q.BPW + q.P - 1) / q.P) * q.BPW : tiles_max * q.GT;
-  q.ts_max = q.streamk ? ipc_max / q.G + 2 + nmat : tiles_max * nmat;
+  const int ipc_max = tiles_max * q.GT;
+  q.ts_max = tiles_max * nmat;
   const int MT = M * TILE_N;
   q.xs_stride = K * 2 + 64;
   size_t fixed = 0;
@@ -896,38 +795,16 @@ int make_plan(int N, int K, int group, int nmat, int M, int grid, bool has_norm,
   return LL_OK;
 }
 
-template <int W, int KSP, int BPW, int EPI = -1, int NORM = -1, int MM = 0, int SK = 0>
+template <int W, int KSP, int BPW, int EPI = -1, int NORM = -1, int MM = 0>
 int launch_cfg(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
   static size_t configured = 0;
   if (pl.smem > configured) {
-    if (configured == 0) prefer_max_smem(gemv_int4_kernel<W, KSP, BPW, EPI, NORM, MM, SK>);
-    LL_CUDA(cudaFuncSetAttribute(gemv_int4_kernel<W, KSP, BPW, EPI, NORM, MM, SK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+    if (configured == 0) prefer_max_smem(gemv_int4_kernel<W, KSP, BPW, EPI, NORM, MM>);
+    LL_CUDA(cudaFuncSetAttribute(gemv_int4_kernel<W, KSP, BPW, EPI, NORM, MM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
     configured = pl.smem;
   }
-  LL_CUDA(launch(gemv_int4_kernel<W, KSP, BPW, EPI, NORM, MM, SK>, dim3(pl.P), dim3((W + 1) * 32), pl.smem, st, pdl, p));
+  LL_CUDA(launch(gemv_int4_kernel<W, KSP, BPW, EPI, NORM, MM>, dim3(pl.P), dim3((W + 1) * 32), pl.smem, st, pdl, p));
   return LL_OK;
-}
-
-// neighbour stream-K scratch: one hand-over slot and one flag per CTA, per device, allocated outside stream capture on
-// first use (kernels of different streams would share it: the switch is for single-stream decode)
-struct SkScratch { float* part; int32_t* flag; int ctas; };
-SkScratch g_sk[16] = {};
-bool sk_scratch(int ctas, cudaStream_t st, float** part, int32_t** flag) {
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return false;
-  SkScratch& k = g_sk[dev];
-  if (k.part == nullptr || k.ctas < ctas) {
-    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
-    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return false;
-    if (k.part != nullptr) return false;  // never re-allocate under captured graphs that hold the old pointers
-    const int n = ctas < 256 ? 256 : ctas;
-    if (cudaMalloc(&k.part, (size_t)n * 2 * MAXM * TILE_N * sizeof(float)) != cudaSuccess) { k.part = nullptr; return false; }
-    if (cudaMalloc(&k.flag, (size_t)n * 32 * sizeof(int32_t)) != cudaSuccess) { cudaFree(k.part); k.part = nullptr; return false; }
-    cudaMemset(k.flag, 0, (size_t)n * 32 * sizeof(int32_t));
-    k.ctas = n;
-  }
-  *part = k.part; *flag = k.flag;
-  return true;
 }
 
 // LLB200_GEMV_SPECIALISE: 0 = the generic kernel, 1 = epilogue / norm as constants, 2 (default) = and batch 1 as a constant
@@ -945,15 +822,6 @@ int launch_plan(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
   // the decode chain's configuration (batch <= 2, group % 128 == 0): one kernel per layer kind
   if (pl.W == 8 && pl.KSP == 4 && pl.BPW == 2 && specialise_level() > 0) {
     const bool norm = p.norm_w != nullptr;
- 
-    if (pl.streamk) {
-#define SPEC_SK(e, n) \
-  if (p.epilogue == e && norm == (n != 0)) return launch_cfg<8, 4, 2, e, n, 1, 1>(p, pl, pdl, st)
-      SPEC_SK(LL_EPI_ROPE_KV, 1); SPEC_SK(LL_EPI_RESIDUAL, 0); SPEC_SK(LL_EPI_SWIGLU, 1); SPEC_SK(LL_EPI_STORE, 1); SPEC_SK(LL_EPI_STORE, 0);
-#undef SPEC_SK
-      set_error("int4 GEMV: no stream-K kernel for epilogue %d", p.epilogue);
-      return LL_ERR_UNSUPPORTED;
-    }
     const bool m1 = p.M == 1 && specialise_level() > 1;
 #define SPEC(e, n)                                                              \
   if (p.epilogue == e && norm == (n != 0))                                      \
@@ -1045,17 +913,10 @@ int ll_int4_gemv(const ll_gemv_args* a, ll_stream stream) {
   }
   cudaStream_t st = (cudaStream_t)stream;
   Plan pl;
-  const bool want_sk = streamk_requested() && specialise_level() > 0 && a->epilogue != LL_EPI_PUSH;
-  if (int r = make_plan(a->N, a->K, a->group, nmat, a->M, a->grid, a->norm_weight != nullptr, &pl, want_sk)) return r;
-  float* sk_part = nullptr;
-  int32_t* sk_flag = nullptr;
-  if (pl.streamk && !sk_scratch(pl.P + 1, st, &sk_part, &sk_flag)) {  // no scratch (first call under capture): whole tiles
-    if (int r = make_plan(a->N, a->K, a->group, nmat, a->M, a->grid, a->norm_weight != nullptr, &pl, false)) return r;
-  }
+  if (int r = make_plan(a->N, a->K, a->group, nmat, a->M, a->grid, a->norm_weight != nullptr, &pl)) return r;
 
   Params p;
   memset(&p, 0, sizeof(p));
-  p.sk_part = sk_part; p.sk_flag = sk_flag;
   p.w[0] = a->w; p.w[1] = a->w2;
   p.nmat = nmat; p.N = a->N; p.K = a->K; p.group = a->group; p.M = a->M;
   p.G = pl.G; p.GT = pl.GT; p.ntiles = pl.ntiles; p.I = pl.I;

@@ -80,13 +80,13 @@ EXPORTS = {
     "ll_decode_attn_scratch_bytes": ([i32, i32, i32, i32], sz_t),
     "ll_silu_mul": ([vp, vp, vp, i32, sz_t, vp], C.c_int),
     "ll_add": ([vp, vp, vp, i32, sz_t, vp], C.c_int),
-    "ll_advance_pos": ([vp, i32, vp], C.c_int),
-    "ll_set_pos": ([vp, vp, i32, vp], C.c_int),
+    "ll_advance_pos": ([vp, i32, i32, vp], C.c_int),
+    "ll_set_pos": ([vp, vp, i32, i32, vp], C.c_int),
     "ll_apply_rope": ([vp, vp, vp, i32, i32, i32, i32, i32, vp], C.c_int),
 }
 _fn = {name: _proto(name, a, r) for name, (a, r) in EXPORTS.items()}
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 if _fn["ll_abi_version"]() != ABI_VERSION:
     raise ImportError("libllb200.so ABI version mismatch; rebuild with lit-llama-ja_b200/build.py")
 

@@ -299,7 +299,7 @@ class DecodeEngine:
 
     def _run_sampled(self, temperature, top_k):
         self._draw(temperature, top_k)
-        N.call("ll_advance_pos", N.ptr(self.pos), self.S, N.stream())
+        N.call("ll_advance_pos", N.ptr(self.pos), self.S, self.rope.shape[0], N.stream())
         self._run_step()
         self.n_launches += 2
 
@@ -312,6 +312,11 @@ class DecodeEngine:
         self.out_tokens[:n] = prompt
         self.logits.copy_(last_logits.reshape(1, -1))
         self.u[:n_draws].uniform_()
+        if self.tp:
+            # every rank must draw the same tokens from its (identical) logits: rank 0's uniforms are the ones used,
+            # however the ranks' generators were seeded or advanced
+            grp = self.tp_group
+            dist.broadcast(self.u[:n_draws], src=dist.get_global_rank(grp, 0) if grp is not None else 0, group=grp)
         self.draw.zero_()
         self.pos.copy_(torch.tensor([n - 1, (n - 1) % self.S, min(n, self.S)], dtype=torch.int32), non_blocking=True)
         return True
@@ -327,7 +332,7 @@ class DecodeEngine:
         # run the two extra kernels once outside capture (their first launch loads them)
         self.pos.zero_()
         self._draw(temperature, top_k)
-        N.call("ll_advance_pos", N.ptr(self.pos), self.S, N.stream())
+        N.call("ll_advance_pos", N.ptr(self.pos), self.S, self.rope.shape[0], N.stream())
         self.pos.zero_()
         self.draw.zero_()
         torch.cuda.synchronize()
@@ -349,7 +354,10 @@ class DecodeEngine:
 
     def forward_token(self, idx: torch.Tensor, input_pos: torch.Tensor) -> torch.Tensor:
         """``LLaMA.forward(idx[B,1], max_seq_length, input_pos[1])`` (ref: model.py:84-128)."""
+        if input_pos.device.type == "cpu":   # checked on the host when it costs no synchronisation (ref model.py:101 raises)
+            assert 0 <= int(input_pos[0]) < self.rope.shape[0], f"input_pos {int(input_pos[0])} outside the RoPE table ({self.rope.shape[0]} rows)"
+            input_pos = input_pos.to(self.tok.device)
         self.tok.copy_(idx.reshape(-1))
-        N.call("ll_set_pos", N.ptr(self.pos), N.ptr(input_pos.to(torch.int64)), self.S, N.stream())
+        N.call("ll_set_pos", N.ptr(self.pos), N.ptr(input_pos.to(torch.int64)), self.S, self.rope.shape[0], N.stream())
         self.step()
         return self.logits.clone().view(self.B, 1, -1)

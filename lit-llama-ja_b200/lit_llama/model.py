@@ -283,7 +283,7 @@ class LLaMA(nn.Module):
             pos_ids = input_pos.to(torch.int32)
             if T == 1:
                 pos3 = torch.empty(3, dtype=torch.int32, device=dev)
-                N.call("ll_set_pos", N.ptr(pos3), N.ptr(input_pos.to(torch.int64)), max_seq_length, N.stream())
+                N.call("ll_set_pos", N.ptr(pos3), N.ptr(input_pos.to(torch.int64)), max_seq_length, block_size, N.stream())
                 pos_ids, slots = pos3[0:1], pos3[1:2]
                 if self.config.head_size not in (32, 64, 128):   # SDPA branch needs an explicit mask
                     mask = (torch.arange(max_seq_length, device=dev) < pos3[2]).view(1, 1, 1, -1)

@@ -43,9 +43,10 @@ class HFTokenizer:
         from tokenizers import Tokenizer as _HF
 
         self.processor = _HF.from_file(str(model_path))
-        self.bos_id = self.processor.token_to_id("<s>")
-        self.eos_id = self.processor.token_to_id("</s>")
-        self.pad_id = self.processor.token_to_id("<pad>")
+        # the fork's vocabulary starts ["<PAD>", "<BOS>", "<EOS>", "<UNK>", "<MASK>"]: fixed ids (ref tokenizer.py:56-61)
+        self.bos_id = 1
+        self.eos_id = 2
+        self.pad_id = 0
 
     @property
     def vocab_size(self) -> int:
@@ -54,13 +55,13 @@ class HFTokenizer:
     def encode(self, string: str, bos: bool = True, eos: bool = False, max_length: int = -1, pad: bool = False,
                device: Optional[torch.device] = None) -> torch.Tensor:
         ids = self.processor.encode(string).ids
-        if bos and self.bos_id is not None:
+        if bos:
             ids = [self.bos_id] + ids
-        if eos and self.eos_id is not None:
+        if eos:
             ids = ids + [self.eos_id]
         if max_length > 0:
             ids = ids[:max_length]
-        if pad and len(ids) < max_length and self.pad_id is not None:
+        if pad and len(ids) < max_length:
             ids = ids + [self.pad_id] * (max_length - len(ids))
         return torch.tensor(ids, dtype=torch.int, device=device)
 

@@ -194,23 +194,6 @@ def test_int4_gemv_forced_grid_matches():
     assert all(np.array_equal(outs[0], o) for o in outs[1:])
 
 
-@pytest.mark.skipif(os.environ.get("LLB200_GEMV_STREAMK") != "1",
-                    reason="opt-in split of the int4 GEMV: run the suite with LLB200_GEMV_STREAMK=1 to cover it")
-@pytest.mark.parametrize("N,K", [(4096, 4096), (4096, 11008), (12288, 4096)])
-def test_int4_gemv_streamk_meets_the_exact_contract(N, K):
-    """Neighbour stream-K (a tile shared by two CTAs, handed over through global memory): same numerics contract as the
-    whole-tile split, and the same bits run to run (fixed order of the two parts)."""
-    tile = 128
-    packed, s, z = _bf16_layer(N, K, tile, 11)
-    lin = make_lin(N, K, 4, tile, s, z, "bf16", packed)
-    xn = OQ.bf16_round(np.random.RandomState(4).randn(1, K).astype(np.float32))
-    x = torch.from_numpy(xn).to(DEV, torch.bfloat16)
-    y = lin(x).float().cpu().numpy()
-    exact_close(y, xn, packed, s, z, tile)
-    for _ in range(3):
-        assert np.array_equal(y, lin(x).float().cpu().numpy())
-
-
 def test_simt_linear_fp32_8bit_and_bias():
     r = np.random.RandomState(3)
     N_, K, bits, tile = 96, 160, 8, 32

@@ -86,52 +86,6 @@ def test_cpu_compute_fails_loudly():
         m(torch.zeros(1, 4, dtype=torch.long))
 
 
-# ----------------------------------------------------------------------------- neighbour stream-K bookkeeping
-def _streamk_ranges(ntiles, G, nmat, P, BPW=2):
-    """The index arithmetic of gemv_int4_kernel<..., SK = 1> (csrc/gemv_int4.cu), restated: per CTA the item range, the
-    tiles whose epilogue it runs, the (tile, matrix) sums it publishes for CTA c-1 and the ones it takes from CTA c+1."""
-    GT = nmat * G
-    U = ntiles * GT // BPW
-    out = []
-    for c in range(P):
-        i0, i1 = (c * U // P) * BPW, ((c + 1) * U // P) * BPW
-        vt_first, vt_last = i0 // G, (i1 - 1) // G
-        t_front, t_back = i0 // GT, (i1 - 1) // GT
-        front, back = i0 != t_front * GT, i1 != (t_back + 1) * GT
-        out.append(dict(i0=i0, i1=i1, vt_first=vt_first, t_back=t_back, t_front=t_front, front=front, back=back,
-                        tiles=range(vt_first // nmat + (1 if front else 0), vt_last // nmat + 1),
-                        publishes=list(range(vt_first, (t_front + 1) * nmat)) if front else [],
-                        takes=list(range(i1 // G, (t_back + 1) * nmat)) if back else []))
-    return out
-
-
-@pytest.mark.parametrize("ntiles,G,nmat,P", [(256, 32, 1, 148), (768, 32, 1, 148), (688, 32, 2, 148), (256, 86, 1, 148),
-                                             (2000, 32, 1, 148), (864, 40, 2, 148), (149, 32, 1, 148), (512, 64, 1, 132)])
-def test_streamk_split_invariants(ntiles, G, nmat, P):
-    """Every item is computed once, every tile has one epilogue owner and at most one more contributor, and what CTA c+1
-    publishes is exactly what CTA c takes (the opt-in LLB200_GEMV_STREAMK=1 split of the int4 GEMV)."""
-    GT = nmat * G
-    r = _streamk_ranges(ntiles, G, nmat, P)
-    assert r[0]["i0"] == 0 and r[-1]["i1"] == ntiles * GT and not r[0]["front"] and not r[-1]["back"]
-    owner = {}
-    for c, k in enumerate(r):
-        assert k["i1"] - k["i0"] >= GT                      # host precondition: a tile has at most two contributors
-        for t in k["tiles"]:
-            assert t not in owner
-            owner[t] = c
-    assert sorted(owner) == list(range(ntiles))
-    for c in range(P - 1):
-        assert r[c]["i1"] == r[c + 1]["i0"]
-        assert r[c]["back"] == r[c + 1]["front"]
-        assert r[c]["takes"] == r[c + 1]["publishes"]
-    for t, c in owner.items():
-        lo, hi = t * GT, (t + 1) * GT
-        covered = min(hi, r[c]["i1"]) - max(lo, r[c]["i0"])
-        if r[c]["back"] and t == r[c]["t_back"]:
-            covered += min(hi, r[c + 1]["i1"]) - max(lo, r[c + 1]["i0"])
-        assert covered == GT
-
-
 # ----------------------------------------------------------------------------- bench.py contract (reference arm, CPU)
 def test_bench_reference_arm_prints_the_contract_line():
     """`bench.py --impl reference` runs on the host cores only and prints ONE JSON line with the keys the driver reads."""
