@@ -480,6 +480,10 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
 #endif
   };
 
+#ifdef LLB_LOOPCLK  // tuning build: cycles each consumer warp spends waiting for its chunk vs in the whole loop
+  long long lc_wait = 0;
+  const long long lc_t0 = clock64();
+#endif
   int it = i0 + warp * BPW;  // first item of this warp in the current chunk
   int vt = it / G, gk = it - vt * G;
   int slot = 0;
@@ -495,7 +499,13 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
       cur_vt = vt;
       out[0] = out[1] = out[2] = out[3] = 0.f;
     }
+#ifdef LLB_LOOPCLK
+    const long long lc_a = clock64();
+#endif
     mbar_wait_u32(full_u + slot * 8, phase);
+#ifdef LLB_LOOPCLK
+    lc_wait += clock64() - lc_a;
+#endif
     if (valid) {
       const uint32_t blk0 = ring_u + (uint32_t)(slot * CHB);
       float t[BPW][4];
@@ -558,6 +568,13 @@ __global__ void __launch_bounds__((W + 1) * 32, (W >= 12 ? 1 : 2)) gemv_int4_ker
     }
   }
   if (cur_vt >= 0) flush(cur_vt);
+#ifdef LLB_LOOPCLK
+  if (p.trace != nullptr && lane == 0) {
+    atomicAdd(&p.trace[blockIdx.x * 16 + 11], (unsigned long long)lc_wait);
+    atomicAdd(&p.trace[blockIdx.x * 16 + 12], (unsigned long long)(clock64() - lc_t0));
+    if (warp == 0) p.trace[blockIdx.x * 16 + 13] = (unsigned long long)nch;
+  }
+#endif
   TRACE(4);
   consumer_sync(NCONS);
 
@@ -818,17 +835,25 @@ int specialise_level() {
   return lv;
 }
 
+// debug: launches per specialised kernel [epilogue][fused norm][batch-1 constant] and of the generic kernels (last entry);
+// read by the tests to assert WHICH instantiations a model-level run exercised (ll_debug_gemv_counts, not in the public header)
+int g_spec_counts[5][2][2] = {};
+int g_generic_count = 0;
+
 int launch_plan(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
   // the decode chain's configuration (batch <= 2, group % 128 == 0): one kernel per layer kind
   if (pl.W == 8 && pl.KSP == 4 && pl.BPW == 2 && specialise_level() > 0) {
     const bool norm = p.norm_w != nullptr;
     const bool m1 = p.M == 1 && specialise_level() > 1;
 #define SPEC(e, n)                                                              \
-  if (p.epilogue == e && norm == (n != 0))                                      \
-    return m1 ? launch_cfg<8, 4, 2, e, n, 1>(p, pl, pdl, st) : launch_cfg<8, 4, 2, e, n>(p, pl, pdl, st)
+  if (p.epilogue == e && norm == (n != 0)) {                                    \
+    ++g_spec_counts[e][n][m1 ? 1 : 0];                                          \
+    return m1 ? launch_cfg<8, 4, 2, e, n, 1>(p, pl, pdl, st) : launch_cfg<8, 4, 2, e, n>(p, pl, pdl, st); \
+  }
     SPEC(LL_EPI_ROPE_KV, 1); SPEC(LL_EPI_RESIDUAL, 0); SPEC(LL_EPI_SWIGLU, 1); SPEC(LL_EPI_STORE, 1); SPEC(LL_EPI_STORE, 0);
 #undef SPEC
   }
+  ++g_generic_count;
 #define CFG(w, k, b) \
   if (pl.W == w && pl.KSP == k && pl.BPW == b) return launch_cfg<w, k, b>(p, pl, pdl, st)
   CFG(12, 4, 1); CFG(8, 4, 2); CFG(12, 4, 2); CFG(8, 4, 1); CFG(16, 4, 1); CFG(16, 4, 2); CFG(4, 4, 1); CFG(4, 4, 2);
@@ -878,6 +903,19 @@ int ll_int4_prepare(const uint8_t* qw, const void* scales, const void* zeros, in
 /* debug (not in the public header): stage time stamps of the next `launches` GEMV launches */
 __attribute__((visibility("default"))) void ll_debug_gemv_trace(unsigned long long* buf, int launches) {
   g_trace = buf; g_trace_launches = launches; g_trace_idx = 0;
+}
+
+/* debug (not in the public header): out[21] = launches per specialised kernel [epilogue 0..4][norm 0/1][batch-1 0/1], then
+ * the generic kernels; counted since the last reset */
+__attribute__((visibility("default"))) void ll_debug_gemv_counts(int32_t* out, int reset) {
+  if (out != nullptr) {
+    memcpy(out, g_spec_counts, sizeof(g_spec_counts));
+    out[20] = g_generic_count;
+  }
+  if (reset) {
+    memset(g_spec_counts, 0, sizeof(g_spec_counts));
+    g_generic_count = 0;
+  }
 }
 
 int ll_int4_gemv_plan(int N, int K, int group, int nmat, int M, int grid, size_t* smem_bytes, int32_t* ctas) {

@@ -112,9 +112,20 @@ class QLinear:
     bits: int = 4
     tile_cols: int = -1
     bias: Optional[np.ndarray] = None
+    cache: bool = False   # keep the de-quantised weight between calls (7B-size layers over many decode steps)
+    _w: dict = field(default_factory=dict, repr=False)
 
     def __call__(self, x, dtype):
-        return Q.linear_forward(x, self.qw, self.scales, self.zeros, self.bias, self.bits, self.tile_cols, dtype)
+        if not self.cache:
+            return Q.linear_forward(x, self.qw, self.scales, self.zeros, self.bias, self.bits, self.tile_cols, dtype)
+        # same arithmetic as Q.linear_forward (quantization.py:420-421) with get_weight() evaluated once
+        if dtype not in self._w:
+            self._w[dtype] = np.ascontiguousarray(Q.get_weight(self.qw, self.scales, self.zeros, self.bits, self.tile_cols, dtype).T)
+        xr = Q.rd(x, dtype)
+        y = xr.reshape(-1, xr.shape[-1]).astype(F32) @ self._w[dtype]
+        if self.bias is not None:
+            y = y + np.asarray(self.bias, dtype=F32)
+        return Q.rd(y, dtype).reshape(*xr.shape[:-1], self._w[dtype].shape[1])
 
 
 @dataclass

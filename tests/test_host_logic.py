@@ -95,8 +95,11 @@ def test_bench_reference_arm_prints_the_contract_line():
     from pathlib import Path
 
     root = Path(__file__).resolve().parent.parent
+    import os
+
+    env = dict(os.environ, LLB200_BENCH_MODEL="tiny", LLB200_BENCH_PROMPT="16", LLB200_BENCH_NEW="8", OMP_NUM_THREADS="1")
     out = subprocess.run([sys.executable, str(root / "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
-                         capture_output=True, text=True, timeout=600, cwd=root)
+                         capture_output=True, text=True, timeout=600, cwd=root, env=env)
     assert out.returncode == 0, out.stderr[-2000:]
     lines = [ln for ln in out.stdout.splitlines() if ln.startswith("{")]
     assert len(lines) == 1
@@ -106,3 +109,5 @@ def test_bench_reference_arm_prints_the_contract_line():
     assert d["cpu_baseline"]["kind"] in ("port", "reference") and d["cpu_baseline"]["cores"] >= 1
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0 and d["e2e"]["value"] == d["value"]
     assert "workload" in d["config"]
+    # all the host threads, whatever OMP_NUM_THREADS torchrun exported; and none of this repo's libraries in that process
+    assert d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
