@@ -96,7 +96,17 @@ LL_API size_t ll_int4_stream_bytes(int N, int K, int group);
  * (device int32) is set to 1 unless every scale and every (16 + zero) is exactly representable
  * in bf16 (then the caller must use ll_qlinear_simt). */
 LL_API int ll_int4_prepare(const uint8_t* qw, const void* scales, const void* zeros, int param_dtype, uint8_t* stream_out,
-                    int N, int K, int group, int32_t* status, ll_stream stream);
+                    int N, int K, int group, int kind, int32_t* status, ll_stream stream);
+
+/* Stream kinds (same size, same tile / block order; they differ in how a block's nibbles are arranged):
+ *   LL_STREAM_BF16: words are mma.m16n8k16 bf16 A fragments (nibble i at bit 3 + 4 i); tail (scale, -(16 + zero)); M = 1..8.
+ *   LL_STREAM_U8:   words are mma.m16n8k32 u8 A fragment pairs (column g in the low nibbles, g + 8 in the high nibbles);
+ *                   tail (scale, -zero); the batch-1 decode kernel (activations as four exact base-256 digit planes).
+ * ll_int4_stream_kind() names the kind the GEMV wants for a shape and batch: prepare that one and pass it in
+ * ll_gemv_args.stream_kind. */
+#define LL_STREAM_BF16 0
+#define LL_STREAM_U8 1
+LL_API int ll_int4_stream_kind(int N, int K, int group, int M);
 
 #define LL_EPI_STORE 0    /* y = bf16(acc (+bias)) */
 #define LL_EPI_RESIDUAL 1 /* y (residual stream, in place) = bf16(y + bf16(acc)) */
@@ -133,6 +143,7 @@ typedef struct ll_gemv_args {
   uint64_t push_dst[8];
   uint64_t push_cnt[8];
   int32_t push_world;
+  int32_t stream_kind; /* LL_STREAM_* of w / w2 (what ll_int4_prepare was asked for) */
 } ll_gemv_args;
 
 /* Host query: LL_OK if the GEMV takes (N, K, group, nmat, M) (LL_ERR_UNSUPPORTED otherwise, e.g. M*K too

@@ -717,6 +717,499 @@ __global__ void int4_repack_kernel(const uint8_t* __restrict__ qw, const P* __re
 }
 
 
+// ==================================================================================== batch-1 kernel, integer MMA
+// The decode chain's kernel (M = 1, scale groups of a multiple of 128): the same ring / tile split / epilogues as above with
+// a cheaper main loop.  profiles/r02_gemv_experiments.md: the bf16 loop above is bound by instruction ISSUE (ALU-pipe
+// instructions hold the issue port for two cycles: 7 of them per 8 weights + bookkeeping = 24 slots per 32-bit word), not
+// by HBM or the tensor pipe.  Here:
+//  * stream kind 1 (ll_int4_prepare kind = 1): a 32-bit word holds 4 k-consecutive nibbles of output column g in the LOW
+//    nibbles of its bytes and the same 4 k of column g + 8 in the HIGH nibbles, so `w & 0x0F0F0F0F` and
+//    `(w >> 4) & 0x0F0F0F0F` ARE two A-fragment registers of mma.m16n8k32.u8.s8: 3 ALU instructions per 8 weights, one
+//    MMA per 16 weights per lane.  Tail per block as before, with -zero in place of -(16 + zero).
+//  * the activation row is turned into FOUR signed base-256 digit planes of x * 2^sh (sh per 128-element k-block from the
+//    block's largest magnitude; exact for every element within 2^22 of it) and the digits are the first four B COLUMNS of
+//    the same MMA: Sum_k q x = Sum_d 256^d (q . digit_d) with every product and sum exact in int32; the digits of a lane pair
+//    are combined in integers, converted once per block and folded with the group scale and zero in fp32.  No (16 + q)
+//    offset, so no cancellation: this path is closer to the exact sum than the bf16 one.
+//  * x staging costs one more shuffle reduction per block (its exponent) and the digit transposition; no extra barrier.
+__device__ __forceinline__ void mma_u8s8_16832(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                               uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t bf16x2_mul(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+// c + a.lo * b.lo and c + a.hi * b.hi with bf16 factors and an fp32 sum: one FHFMA each (native on sm_100a)
+__device__ __forceinline__ float fhfma_lo(uint32_t a, uint32_t b, float c) {
+  float r;
+  asm("{\n\t.reg .b16 al, ah, bl, bh;\n\tmov.b32 {al, ah}, %1;\n\tmov.b32 {bl, bh}, %2;\n\tfma.rn.f32.bf16 %0, al, bl, %3;\n\t}"
+      : "=f"(r) : "r"(a), "r"(b), "f"(c));
+  return r;
+}
+__device__ __forceinline__ float fhfma_hi(uint32_t a, uint32_t b, float c) {
+  float r;
+  asm("{\n\t.reg .b16 al, ah, bl, bh;\n\tmov.b32 {al, ah}, %1;\n\tmov.b32 {bl, bh}, %2;\n\tfma.rn.f32.bf16 %0, ah, bh, %3;\n\t}"
+      : "=f"(r) : "r"(a), "r"(b), "f"(c));
+  return r;
+}
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+  return r;
+}
+
+constexpr int I8_W = 8, I8_BPW = 2, I8_KB = 128;
+constexpr int I8_BLK = I8_KB * 8 + TAIL_BYTES;
+constexpr int I8_CH = I8_W * I8_BPW, I8_CHB = I8_CH * I8_BLK, I8_NCONS = I8_W * 32;
+constexpr uint32_t NIB_LO = 0x0F0F0F0Fu;
+
+template <int EPI, int NORM>
+__global__ void __launch_bounds__((I8_W + 1) * 32, 2) gemv_w4a8_kernel(const __grid_constant__ Params p) {
+  constexpr int W = I8_W, BPW = I8_BPW, KB = I8_KB, BLK = I8_BLK, CH = I8_CH, CHB = I8_CHB, NCONS = I8_NCONS;
+  constexpr int MAX_SLOTS_C = 12;
+  constexpr int MT = TILE_N;  // floats per (tile, matrix) result at batch 1
+  constexpr bool has_norm = NORM != 0;
+  constexpr int epilogue = EPI;
+
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* ring = smem;
+  uint8_t* xs = smem + p.off_xs;                            // 4 digit planes [K + 16] + 128 zero bytes
+  float* rec = reinterpret_cast<float*>(smem + p.off_sx);   // [G][2][2] (scale of the digits, zero-point sum) + 4 zeros
+  float* red = reinterpret_cast<float*>(smem + p.off_red);  // [ts_max][W][16]
+  float* wv = reinterpret_cast<float*>(smem + p.off_wv);    // [W][nmat][16]
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + p.off_bar);
+  uint64_t* empty = full + p.S;
+  __shared__ float s_part[W];
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int P = gridDim.x, c = blockIdx.x;
+  const int i0 = range_start(c, p.ntiles, P) * p.GT;
+  const int i1 = range_start(c + 1, p.ntiles, P) * p.GT;
+  const int nch = (i1 - i0 + CH - 1) / CH;
+  const int G = p.G, S = p.S;
+
+  TRACE(0);
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < S; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], W);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  pdl_launch_dependents();
+
+  if (warp == W) {
+    // =============================== producer warp (as in the bf16 kernel) ===============================
+    if (lane == 0) {
+      const uint64_t pol = policy_evict_first();
+      int slot = 0;
+      uint32_t phase = 1;
+      int it = i0;
+      int vt = it / G, g = it - vt * G;
+      for (int ch = 0; ch < nch; ++ch, ++slot) {
+        if (slot == S) {
+          slot = 0;
+          phase ^= 1u;
+        }
+        if (ch >= S) mbar_wait_u32(smem_u32(&empty[slot]), phase);
+        const int b = min(it + CH, i1);
+        mbar_expect_tx(&full[slot], (uint32_t)(b - it) * BLK);
+        uint8_t* dst = ring + (size_t)slot * CHB;
+        while (it < b) {
+          const int run = min(G - g, b - it);
+          const int mat = p.nmat == 2 ? (vt & 1) : 0, tile = p.nmat == 2 ? (vt >> 1) : vt;
+          const uint8_t* src = p.w[mat] + ((size_t)tile * G + g) * BLK;
+          bulk_load_1d_hint(dst, src, (uint32_t)run * BLK, &full[slot], pol);
+          dst += (size_t)run * BLK;
+          it += run;
+          g += run;
+          if (g == G) {
+            g = 0;
+            ++vt;
+          }
+        }
+      }
+    }
+    return;
+  }
+
+  // ================================= consumer warps =================================
+  const int g = lane >> 2, tig = lane & 3;
+  const int ctid = threadIdx.x;
+  const int vt_first = i0 / G, vt_last = (i1 - 1) / G;
+  const int nvt = vt_last - vt_first + 1;
+  const int vpr = p.K >> 3;
+  const int pstride = p.xs_stride;  // bytes between digit planes (K + 16: neighbouring planes land in different banks)
+
+  uint8_t* nws = smem + p.off_nw;
+  uint64_t* xbar = full + 2 * MAX_SLOTS_C;
+  if (ctid == 0) {
+    mbar_init(&xbar[1], 1);
+    fence_barrier_init();
+    if (has_norm) {
+      mbar_expect_tx(&xbar[1], (uint32_t)p.K * 2);
+      bulk_load_1d(nws, p.norm_w, (uint32_t)p.K * 2, &xbar[1]);
+    }
+  }
+  for (int i = ctid; i < nvt * W * MT; i += NCONS) red[i] = 0.f;
+  if (ctid < 32) *reinterpret_cast<uint32_t*>(xs + 4 * (size_t)pstride + ctid * 4) = 0u;  // zero area of the B fragments
+  if (ctid < 4) rec[(size_t)G * 4 + ctid] = 0.f;                                           // and of the records
+  consumer_sync(NCONS);
+
+  TRACE(1);
+  pdl_wait();
+  TRACE(2);
+  int rope_pos = 0, kv_slot = 0;
+  if (epilogue == LL_EPI_ROPE_KV) {
+    rope_pos = p.pos[0];
+    kv_slot = p.pos[1];
+  }
+
+  // ---- stage x.  One 16-byte piece (8 elements) per thread per pass of 256 pieces; the 16 threads of a half-warp hold
+  //      one 128-element k-block.  A thread's pieces are fetched TOGETHER (one L2 round trip for K <= 16384; longer rows
+  //      in groups of XR pieces).  With the fused RMSNorm the whole row is fetched first (its sum of squares needs all of
+  //      it); the first group stays in registers for the second pass, later groups are fetched again (an L2 hit).
+  //      Arithmetic on packed bf16 pairs (HMUL2.BF16 rounds exactly where the reference's bf16 ops round) and
+  //      fp32 += bf16 * bf16 (FHFMA): a fifth of the instructions of the scalar fp32 form.
+  constexpr int XR = 8;
+  constexpr uint32_t ONE2 = 0x3f803f80u;  // bf16x2 (1, 1)
+  uint4 raw[XR];
+  uint32_t rn2 = 0u;
+  const uint4* xsrc = reinterpret_cast<const uint4*>(p.x);
+  auto fetch = [&](int v0) {
+#pragma unroll
+    for (int j = 0; j < XR; ++j) {
+      const int v = v0 + j * NCONS + ctid;
+      raw[j] = v < vpr ? __ldcg(xsrc + v) : make_uint4(0u, 0u, 0u, 0u);
+    }
+  };
+  fetch(0);
+  if (has_norm) {
+    float ss = 0.f;
+    for (int v0 = 0; v0 < vpr; v0 += XR * NCONS) {
+      uint4 r4[XR];
+      if (v0 == 0) {
+#pragma unroll
+        for (int j = 0; j < XR; ++j) r4[j] = raw[j];
+      } else {
+#pragma unroll
+        for (int j = 0; j < XR; ++j) {
+          const int v = v0 + j * NCONS + ctid;
+          r4[j] = v < vpr ? __ldcg(xsrc + v) : make_uint4(0u, 0u, 0u, 0u);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < XR; ++j) {
+        if (v0 + j * NCONS < vpr) {  // uniform
+          const uint32_t wd[4] = {r4[j].x, r4[j].y, r4[j].z, r4[j].w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const uint32_t sq = bf16x2_mul(wd[e], wd[e]);  // bf16(x * x), ref model.py:280
+            ss = fhfma_lo(sq, ONE2, ss);
+            ss = fhfma_hi(sq, ONE2, ss);
+          }
+        }
+      }
+    }
+    ss = warp_sum(ss);
+    if (lane == 0) s_part[warp] = ss;
+    TRACE(9);
+    consumer_sync(NCONS);
+    float tot = 0.f;
+#pragma unroll
+    for (int w = 0; w < W; ++w) tot += s_part[w];
+    const float mean = bf16r(tot * (1.0f / (float)p.K));
+    const float rn = bf16r(rsqrtf(bf16r(mean + p.eps)));
+    rn2 = (__float_as_uint(rn) >> 16) * 0x00010001u;
+    mbar_wait_u32(smem_u32(&xbar[1]), 0);
+    TRACE(7);
+  }
+  for (int v0 = 0; v0 < vpr; v0 += XR * NCONS) {
+    if (v0 > 0) fetch(v0);
+#pragma unroll
+    for (int j = 0; j < XR; ++j) {
+      if (v0 + j * NCONS >= vpr) continue;  // uniform over the CTA
+      const int v = v0 + j * NCONS + ctid;
+      const bool ok = v < vpr;  // uniform over a half-warp: K is a multiple of 128
+      uint32_t wd[4] = {raw[j].x, raw[j].y, raw[j].z, raw[j].w};
+      if (has_norm) {  // ref model.py:276-283 rounding steps: bf16(w * bf16(x * r))
+        uint4 nraw = make_uint4(0u, 0u, 0u, 0u);
+        if (ok) nraw = *reinterpret_cast<const uint4*>(nws + (size_t)v * 16);
+        const uint32_t nw[4] = {nraw.x, nraw.y, nraw.z, nraw.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) wd[e] = bf16x2_mul(nw[e], bf16x2_mul(wd[e], rn2));
+      }
+      // the block's exponent from the largest magnitude of its 128 elements (16 lanes); the sum of the block for the zero term
+      uint32_t m2 = bf16x2_max(bf16x2_max(wd[0] & 0x7fff7fffu, wd[1] & 0x7fff7fffu), bf16x2_max(wd[2] & 0x7fff7fffu, wd[3] & 0x7fff7fffu));
+      float sum = 0.f;
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        sum = fhfma_lo(wd[e], ONE2, sum);
+        sum = fhfma_hi(wd[e], ONE2, sum);
+      }
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) {
+        m2 = bf16x2_max(m2, __shfl_xor_sync(0xffffffffu, m2, o));
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+      }
+      int ex = (int)max((m2 >> 7) & 0xffu, (m2 >> 23) & 0xffu);  // biased exponent of the largest magnitude: am < 2^(ex - 126)
+      ex = max(ex, 32);                                            // all-zero / denormal blocks: any finite scale will do
+      const uint32_t scale2 = ((uint32_t)(283 - ex) << 7) * 0x00010001u;  // bf16x2 2^(156 - ex): am * scale < 2^30
+      const float inv = __uint_as_float((uint32_t)(ex - 29) << 23);       // 2^-(156 - ex)
+      uint32_t u[8];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int v0i = __float2int_rn(fhfma_lo(wd[e], scale2, 0.f)), v1i = __float2int_rn(fhfma_hi(wd[e], scale2, 0.f));
+        u[2 * e] = ((uint32_t)v0i + 0x00808080u) ^ 0x00808080u;  // bytes = four signed base-256 digits
+        u[2 * e + 1] = ((uint32_t)v1i + 0x00808080u) ^ 0x00808080u;
+      }
+      if (ok) {
+        // 4 x 4 byte transpositions: plane d gets byte d of eight consecutive elements
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const uint32_t a = prmt(u[4 * h], u[4 * h + 1], 0x5140u), b = prmt(u[4 * h], u[4 * h + 1], 0x7362u);
+          const uint32_t cc = prmt(u[4 * h + 2], u[4 * h + 3], 0x5140u), d = prmt(u[4 * h + 2], u[4 * h + 3], 0x7362u);
+          uint8_t* dst = xs + (size_t)v * 8 + h * 4;
+          *reinterpret_cast<uint32_t*>(dst) = prmt(a, cc, 0x5410u);
+          *reinterpret_cast<uint32_t*>(dst + pstride) = prmt(a, cc, 0x7632u);
+          *reinterpret_cast<uint32_t*>(dst + 2 * (size_t)pstride) = prmt(b, d, 0x5410u);
+          *reinterpret_cast<uint32_t*>(dst + 3 * (size_t)pstride) = prmt(b, d, 0x7632u);
+        }
+        if ((lane & 15) == 0) {  // record of the block: lanes tig = 0 take (inv, sum x), lanes tig = 1 take (inv * 2^16, 0)
+          float4 r;
+          r.x = inv;
+          r.y = sum;
+          r.z = inv * 65536.f;
+          r.w = 0.f;
+          *reinterpret_cast<float4*>(rec + (size_t)(v >> 4) * 4) = r;
+        }
+      }
+    }
+  }
+  TRACE(10);
+  consumer_sync(NCONS);
+  TRACE(3);
+
+  // epilogue operands that do not depend on this kernel's sums, fetched for this warp's first tile behind the main loop
+  const int nmat = p.nmat;
+  const int T_first = vt_first / nmat, T_last = vt_last / nmat;
+  auto load_pre = [&](int T, float& pre, float2& cs) {
+    const int n0 = T * TILE_N;
+    if (epilogue == LL_EPI_RESIDUAL) {
+      if (lane < MT) pre = __bfloat162float(p.y[n0 + lane]);
+    } else if (epilogue == LL_EPI_STORE && p.bias != nullptr) {
+      pre = __bfloat162float(p.bias[n0 + (lane & 15)]);
+    } else if (epilogue == LL_EPI_ROPE_KV) {
+      const int E = p.N / 3, hs = p.head_size;
+      const int n = n0 + 2 * (lane & 7);
+      const int part = n / E, d = (n - part * E) % hs;
+      if (lane < TILE_N / 2 && part < 2)
+        cs = *reinterpret_cast<const float2*>(p.rope + ((size_t)rope_pos * (hs / 2) + d / 2) * 2);
+    }
+  };
+  float pre0 = 0.f;
+  float2 cs0 = make_float2(1.f, 0.f);
+  if (T_first + warp <= T_last) load_pre(T_first + warp, pre0, cs0);
+
+  // ---- main loop
+  // per-lane addressing: lanes with g < 4 read digit plane g (32 bytes per block at tig * 32), the others a zero area with
+  // stride 0; lanes with tig < 2 read their record, the others a zero record with stride 0
+  const uint32_t xs_lane = smem_u32(xs) + (g < 4 ? (uint32_t)(g * pstride + tig * 32) : (uint32_t)(4 * pstride + tig * 32));
+  const uint32_t xs_step = g < 4 ? (uint32_t)KB : 0u;
+  const uint32_t rec_lane = smem_u32(rec) + (tig < 2 ? (uint32_t)(tig * 8) : (uint32_t)(G * 16));
+  const uint32_t rec_step = tig < 2 ? 16u : 0u;
+  const uint32_t ring_u = smem_u32(ring) + (uint32_t)(warp * BPW * BLK);
+  const uint32_t full_u = smem_u32(full), empty_u = smem_u32(empty);
+
+  float out0 = 0.f, out1 = 0.f;  // columns g and g + 8 of the current tile, this lane's digit pair
+  int cur_vt = -1;
+  auto flush = [&](int vt) {
+    float v0 = out0, v1 = out1;
+    v0 += __shfl_xor_sync(0xffffffffu, v0, 1);
+    v1 += __shfl_xor_sync(0xffffffffu, v1, 1);
+    v0 += __shfl_xor_sync(0xffffffffu, v0, 2);
+    v1 += __shfl_xor_sync(0xffffffffu, v1, 2);
+    if (tig == 0) {
+      float* r = red + ((size_t)(vt - vt_first) * W + warp) * MT;
+      r[g] = v0;
+      r[g + 8] = v1;
+    }
+  };
+#ifdef LLB_LOOPCLK
+  long long lc_wait = 0;
+  const long long lc_t0 = clock64();
+#endif
+  int it = i0 + warp * BPW;
+  int vt = it / G, gk = it - vt * G;
+  int slot = 0;
+  uint32_t phase = 0;
+  for (int ch = 0; ch < nch; ++ch) {
+    const bool valid = it < i1;
+    if (valid && vt != cur_vt) {  // the two blocks a warp takes from a chunk share their tile (G is even)
+      if (cur_vt >= 0) flush(cur_vt);
+      cur_vt = vt;
+      out0 = out1 = 0.f;
+    }
+#ifdef LLB_LOOPCLK
+    const long long lc_a = clock64();
+#endif
+    mbar_wait_u32(full_u + slot * 8, phase);
+#ifdef LLB_LOOPCLK
+    lc_wait += clock64() - lc_a;
+#endif
+    if (valid) {
+      const uint32_t blk0 = ring_u + (uint32_t)(slot * CHB);
+      int d[BPW][4];
+      uint2 sz[BPW], rc[BPW];
+#pragma unroll
+      for (int b = 0; b < BPW; ++b) {
+        const uint32_t blk = blk0 + b * BLK;
+        const uint4 w0 = lds128(blk + lane * 16), w1 = lds128(blk + 512 + lane * 16);
+        const uint32_t xk = xs_lane + (uint32_t)(gk + b) * xs_step;
+        const uint4 xa = lds128(xk), xb = lds128(xk + 16);
+        sz[b] = lds64(blk + KB * 8 + g * 8);
+        rc[b] = lds64(rec_lane + (uint32_t)(gk + b) * rec_step);
+        d[b][0] = d[b][1] = d[b][2] = d[b][3] = 0;
+        mma_u8s8_16832(d[b], w0.x & NIB_LO, (w0.x >> 4) & NIB_LO, w0.y & NIB_LO, (w0.y >> 4) & NIB_LO, xa.x, xa.y);
+        mma_u8s8_16832(d[b], w0.z & NIB_LO, (w0.z >> 4) & NIB_LO, w0.w & NIB_LO, (w0.w >> 4) & NIB_LO, xa.z, xa.w);
+        mma_u8s8_16832(d[b], w1.x & NIB_LO, (w1.x >> 4) & NIB_LO, w1.y & NIB_LO, (w1.y >> 4) & NIB_LO, xb.x, xb.y);
+        mma_u8s8_16832(d[b], w1.z & NIB_LO, (w1.z >> 4) & NIB_LO, w1.w & NIB_LO, (w1.w >> 4) & NIB_LO, xb.z, xb.w);
+      }
+#pragma unroll
+      for (int b = 0; b < BPW; ++b) {
+        // this lane's two digits of each column, combined in integers (|sum| < 2^26), converted once
+        const float f0 = (float)(d[b][0] + (d[b][1] << 8)), f1 = (float)(d[b][2] + (d[b][3] << 8));
+        const float s0 = __uint_as_float(sz[b].x << 16), zn0 = __uint_as_float(sz[b].x & 0xffff0000u);
+        const float s1 = __uint_as_float(sz[b].y << 16), zn1 = __uint_as_float(sz[b].y & 0xffff0000u);
+        const float e = __uint_as_float(rc[b].x), zs = __uint_as_float(rc[b].y);
+        // scale * (2^-sh 256^(2 tig) digits  -  zero * sum x)
+        out0 = fmaf(s0, fmaf(zn0, zs, e * f0), out0);
+        out1 = fmaf(s1, fmaf(zn1, zs, e * f1), out1);
+      }
+    }
+    __syncwarp();
+    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty_u + slot * 8) : "memory");
+    it += CH;
+    gk += CH;
+    while (gk >= G) {
+      gk -= G;
+      ++vt;
+    }
+    if (++slot == S) {
+      slot = 0;
+      phase ^= 1u;
+    }
+  }
+  if (cur_vt >= 0) flush(cur_vt);
+#ifdef LLB_LOOPCLK
+  if (p.trace != nullptr && lane == 0) {
+    atomicAdd(&p.trace[blockIdx.x * 16 + 11], (unsigned long long)lc_wait);
+    atomicAdd(&p.trace[blockIdx.x * 16 + 12], (unsigned long long)(clock64() - lc_t0));
+    if (warp == 0) p.trace[blockIdx.x * 16 + 13] = (unsigned long long)nch;
+  }
+#endif
+  TRACE(4);
+  consumer_sync(NCONS);
+
+  TRACE(5);
+  // ---- fused epilogue, one warp per tile (every tile is complete inside its CTA); rounding steps as in the bf16 kernel
+  float* vals = wv + (size_t)warp * nmat * MT;
+  for (int T = T_first + warp; T <= T_last; T += W) {
+    const int n0 = T * TILE_N;
+    float pre = pre0;
+    float2 cs = cs0;
+    if (T != T_first + warp) load_pre(T, pre, cs);
+    if (lane < nmat * MT) {
+      const float* r = red + (size_t)(T * nmat - vt_first) * W * MT + (lane / MT) * W * MT + (lane % MT);
+      float v = 0.f;
+#pragma unroll
+      for (int w = 0; w < W; ++w) v += r[w * MT];
+      vals[lane] = v;
+    }
+    __syncwarp();
+    if (epilogue == LL_EPI_STORE) {
+      if (lane < MT) p.y[n0 + lane] = __float2bfloat16_rn(vals[lane] + pre);
+    } else if (epilogue == LL_EPI_RESIDUAL) {
+      if (lane < MT) p.y[n0 + lane] = __float2bfloat16_rn(__fadd_rn(pre, bf16r(vals[lane])));   // ref model.py:172-173
+    } else if (epilogue == LL_EPI_ROPE_KV) {
+      const int E = p.N / 3, hs = p.head_size;
+      if (lane < TILE_N / 2) {
+        const int cc = 2 * lane, n = n0 + cc;
+        const int part = n / E, ee = n - part * E, head = ee / hs, d = ee - head * hs;
+        float x0 = bf16r(vals[cc]), x1 = bf16r(vals[cc + 1]);
+        if (part < 2) {
+          const float o0 = __fsub_rn(__fmul_rn(x0, cs.x), __fmul_rn(x1, cs.y));
+          const float o1 = __fadd_rn(__fmul_rn(x1, cs.x), __fmul_rn(x0, cs.y));
+          x0 = o0; x1 = o1;
+        }
+        const __nv_bfloat162 o = __floats2bfloat162_rn(x0, x1);
+        if (part == 0) {
+          *reinterpret_cast<__nv_bfloat162*>(p.y + ee) = o;
+        } else {
+          __nv_bfloat16* cache = part == 1 ? p.k_cache : p.v_cache;
+          *reinterpret_cast<__nv_bfloat162*>(cache + ((size_t)head * p.cache_len + kv_slot) * hs + d) = o;
+        }
+      }
+    } else if (epilogue == LL_EPI_SWIGLU) {
+      if (lane < MT) {
+        const float a = bf16r(vals[lane]), b = bf16r(vals[MT + lane]);
+        const float sl = bf16r(a / (1.0f + expf(-a)));
+        p.y[n0 + lane] = __float2bfloat16_rn(__fmul_rn(sl, b));
+      }
+    }
+    __syncwarp();
+  }
+  TRACE(6);
+}
+
+// stream kind 1: one thread per 32-bit word (and per tail entry)
+template <typename P>
+__global__ void int4_repack_u8_kernel(const uint8_t* __restrict__ qw, const P* __restrict__ scales, const P* __restrict__ zeros,
+                                      uint8_t* __restrict__ out, int N, int K, int group, int32_t* status) {
+  constexpr int KB = I8_KB, BLK = I8_BLK;
+  const int G = K / KB, Gq = K / group;
+  const int words = KB * 2;
+  const int per_blk = words + TILE_N;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long nblk = (long long)(N / TILE_N) * G;
+  if (idx >= nblk * per_blk) return;
+  const long long b = idx / per_blk;
+  const int r = (int)(idx - b * per_blk);
+  const int tile = (int)(b / G), gk = (int)(b - (long long)tile * G);
+  uint8_t* blk = out + (size_t)b * BLK;
+  if (r >= words) {  // tail: entry e -> column tile*16 + (e>>1) + 8*(e&1): (scale, -zero)
+    const int e = r - words;
+    const int n = tile * TILE_N + (e >> 1) + 8 * (e & 1);
+    const int gq = (gk * KB) / group;
+    const float s = dt<P>::ld(scales, (size_t)n * Gq + gq);
+    const float zn = -dt<P>::ld(zeros, (size_t)n * Gq + gq);
+    if (!(bf16r(zn) == zn) || !(bf16r(s) == s)) atomicExch(status, 1);
+    reinterpret_cast<uint32_t*>(blk + KB * 8)[e] = (uint32_t)f32_to_bf16_bits(s) | ((uint32_t)f32_to_bf16_bits(zn) << 16);
+    return;
+  }
+  // word r = (q, lane, j): the lane's word 4 q + j covers k = 32 tig + 4 (4 q + j) + 0..3 of the block
+  const int q = r >> 7, lane = (r & 127) >> 2, j = r & 3;
+  const int g = lane >> 2, tig = lane & 3;
+  const int kbase = gk * KB + 32 * tig + 4 * (4 * q + j);
+  const int n_lo = tile * TILE_N + g, n_hi = n_lo + 8;
+  auto nib = [&](int n, int k) -> uint32_t { return (qw[(size_t)(k >> 1) * N + n] >> ((k & 1) * 4)) & 15u; };
+  uint32_t w = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) w |= (nib(n_lo, kbase + i) << (8 * i)) | (nib(n_hi, kbase + i) << (8 * i + 4));
+  *reinterpret_cast<uint32_t*>(blk + q * 512 + lane * 16 + j * 4) = w;
+}
+
 // ------------------------------------------------------------------------------------ host side
 struct Plan {
   int KB, KSP, BLK, W, BPW;
@@ -835,6 +1328,79 @@ int specialise_level() {
   return lv;
 }
 
+// Plan of the batch-1 integer-MMA kernel (stream kind 1): same tile split and ring as the bf16 kernel; shared memory holds
+// four digit planes of x instead of bf16 rows.
+bool i8_shape_ok(int N, int K, int group, int M) {
+  return M == 1 && group > 0 && group % I8_KB == 0 && K % group == 0 && N % TILE_N == 0 && (K / I8_KB) % I8_BPW == 0;
+}
+
+int make_plan_i8(int N, int K, int group, int nmat, int grid, bool has_norm, Plan* pl) {
+  if (!i8_shape_ok(N, K, group, 1)) {
+    set_error("int4 GEMV (stream kind 1) needs M = 1, N %% 16 == 0, group %% 128 == 0, K %% 256 == 0 (N=%d K=%d group=%d)", N, K, group);
+    return LL_ERR_UNSUPPORTED;
+  }
+  const int sms = sm_count();
+  if (sms <= 0) {
+    set_error("no CUDA device");
+    return LL_ERR_CUDA;
+  }
+  Plan& q = *pl;
+  q.KB = I8_KB; q.KSP = 4; q.BLK = I8_BLK; q.W = I8_W; q.BPW = I8_BPW;
+  q.G = K / I8_KB; q.GT = nmat * q.G; q.ntiles = N / TILE_N;
+  const long long items = (long long)q.ntiles * q.GT;
+  if (items > 0x3fffffff) {
+    set_error("int4 GEMV: too many work items (%lld)", items);
+    return LL_ERR_UNSUPPORTED;
+  }
+  q.I = (int)items;
+  q.P = grid > 0 ? grid : sms;
+  if (q.P > q.ntiles) q.P = q.ntiles;
+  if ((long long)q.ntiles * (q.P + 1) > 0xffffffffLL) {
+    set_error("int4 GEMV: N too large (%d)", N);
+    return LL_ERR_UNSUPPORTED;
+  }
+  const int tiles_max = (q.ntiles + q.P - 1) / q.P;
+  const int ipc_max = tiles_max * q.GT;
+  q.ts_max = tiles_max * nmat;
+  q.xs_stride = K + 16;
+  size_t fixed = 0;
+  auto take = [&](size_t bytes) { size_t o = fixed; fixed += (bytes + 127) & ~(size_t)127; return (int)o; };
+  q.off_xs = take((size_t)4 * q.xs_stride + 128);
+  q.off_sx = take((size_t)q.G * 16 + 16);
+  q.off_red = take((size_t)q.ts_max * q.W * TILE_N * 4);
+  q.off_wv = take((size_t)q.W * nmat * TILE_N * 4);
+  q.off_bar = take((size_t)(2 * MAX_SLOTS + 2) * 8);
+  q.off_nw = take(has_norm ? (size_t)K * 2 : 0);
+  const size_t chb = (size_t)I8_CHB;
+  const int nch_max = (ipc_max + I8_CH - 1) / I8_CH;
+  long s = ((long)SMEM_CORESIDENT - (long)fixed) / (long)chb;
+  if (s < 3 && nch_max > s) s = ((long)SMEM_SOLO - (long)fixed) / (long)chb;
+  if (s > MAX_SLOTS) s = MAX_SLOTS;
+  if (s > nch_max) s = nch_max;
+  if (s < 1 || (s < 2 && nch_max > 1)) {
+    set_error("int4 GEMV: K too large for shared memory (K=%d)", K);
+    return LL_ERR_UNSUPPORTED;
+  }
+  q.S = (int)s;
+  const size_t ring = (size_t)q.S * chb;
+  q.off_xs += (int)ring; q.off_sx += (int)ring; q.off_red += (int)ring;
+  q.off_wv += (int)ring; q.off_bar += (int)ring; q.off_nw += (int)ring;
+  q.smem = ring + fixed;
+  return LL_OK;
+}
+
+template <int EPI, int NORM>
+int launch_i8(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
+  static size_t configured = 0;
+  if (pl.smem > configured) {
+    if (configured == 0) prefer_max_smem(gemv_w4a8_kernel<EPI, NORM>);
+    LL_CUDA(cudaFuncSetAttribute(gemv_w4a8_kernel<EPI, NORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+    configured = pl.smem;
+  }
+  LL_CUDA(launch(gemv_w4a8_kernel<EPI, NORM>, dim3(pl.P), dim3((I8_W + 1) * 32), pl.smem, st, pdl, p));
+  return LL_OK;
+}
+
 // debug: launches per specialised kernel [epilogue][fused norm][batch-1 constant] and of the generic kernels (last entry);
 // read by the tests to assert WHICH instantiations a model-level run exercised (ll_debug_gemv_counts, not in the public header)
 int g_spec_counts[5][2][2] = {};
@@ -864,6 +1430,20 @@ int launch_plan(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
   return LL_ERR_UNSUPPORTED;
 }
 
+int launch_plan_i8(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
+  const bool norm = p.norm_w != nullptr;
+#define SPEC_I8(e, n)                          \
+  if (p.epilogue == e && norm == (n != 0)) {   \
+    ++g_spec_counts[e][n][1];                  \
+    return launch_i8<e, n>(p, pl, pdl, st);    \
+  }
+  SPEC_I8(LL_EPI_ROPE_KV, 1); SPEC_I8(LL_EPI_RESIDUAL, 0); SPEC_I8(LL_EPI_SWIGLU, 1); SPEC_I8(LL_EPI_STORE, 1); SPEC_I8(LL_EPI_STORE, 0);
+  SPEC_I8(LL_EPI_SWIGLU, 0); SPEC_I8(LL_EPI_RESIDUAL, 1); SPEC_I8(LL_EPI_ROPE_KV, 0);
+#undef SPEC_I8
+  set_error("int4 GEMV (stream kind 1): no kernel for epilogue %d", p.epilogue);
+  return LL_ERR_UNSUPPORTED;
+}
+
 }  // namespace
 }  // namespace llb
 
@@ -878,8 +1458,28 @@ size_t ll_int4_stream_bytes(int N, int K, int group) {
 }
 
 int ll_int4_prepare(const uint8_t* qw, const void* scales, const void* zeros, int pdt, uint8_t* out, int N, int K,
-                    int group, int32_t* status, ll_stream stream) {
+                    int group, int kind, int32_t* status, ll_stream stream) {
   LL_CHECK_ARG(qw && scales && zeros && out && status, "null pointer");
+  LL_CHECK_ARG(kind == LL_STREAM_BF16 || kind == LL_STREAM_U8, "bad stream kind %d", kind);
+  if (kind == LL_STREAM_U8) {
+    if (!i8_shape_ok(N, K, group, 1)) {
+      set_error("int4_prepare: stream kind 1 needs group %% 128 == 0, K %% 256 == 0, N %% 16 == 0 (N=%d K=%d group=%d)", N, K, group);
+      return LL_ERR_UNSUPPORTED;
+    }
+    LL_CHECK_ARG(((uintptr_t)out & 15) == 0, "stream buffer must be 16-byte aligned");
+    const long long nblk8 = (long long)(N / TILE_N) * (K / I8_KB);
+    const long long total8 = nblk8 * (I8_KB * 2 + TILE_N);
+    const unsigned blocks8 = (unsigned)((total8 + 255) / 256);
+    cudaStream_t st8 = (cudaStream_t)stream;
+    if (pdt == LL_F32) int4_repack_u8_kernel<float><<<blocks8, 256, 0, st8>>>(qw, (const float*)scales, (const float*)zeros, out, N, K, group, status);
+    else if (pdt == LL_BF16) int4_repack_u8_kernel<__nv_bfloat16><<<blocks8, 256, 0, st8>>>(qw, (const __nv_bfloat16*)scales, (const __nv_bfloat16*)zeros, out, N, K, group, status);
+    else {
+      set_error("int4_prepare: unsupported param dtype %d", pdt);
+      return LL_ERR_UNSUPPORTED;
+    }
+    LL_LAUNCH_OK("int4_repack_u8_kernel");
+    return LL_OK;
+  }
   const int KB = pick_kb(K, group);
   if (KB == 0 || N <= 0 || N % TILE_N != 0 || K % 8 != 0) {
     set_error("int4_prepare: unsupported shape N=%d K=%d group=%d", N, K, group);
@@ -918,10 +1518,21 @@ __attribute__((visibility("default"))) void ll_debug_gemv_counts(int32_t* out, i
   }
 }
 
+int ll_int4_stream_kind(int N, int K, int group, int M) {
+  static int force = -1;  // LLB200_GEMV_KIND=0 keeps the bf16 kernel for batch 1 (tuning / A-B measurements)
+  if (force < 0) {
+    const char* e = getenv("LLB200_GEMV_KIND");
+    force = e ? atoi(e) : 1;
+  }
+  return (force != 0 && i8_shape_ok(N, K, group, M)) ? LL_STREAM_U8 : LL_STREAM_BF16;
+}
+
 int ll_int4_gemv_plan(int N, int K, int group, int nmat, int M, int grid, size_t* smem_bytes, int32_t* ctas) {
   LL_CHECK_ARG(N > 0 && K > 0 && group > 0 && (nmat == 1 || nmat == 2) && M >= 1 && M <= MAXM, "bad plan arguments");
   Plan pl;
-  if (int r = make_plan(N, K, group, nmat, M, grid, true, &pl)) return r;
+  if (ll_int4_stream_kind(N, K, group, M) == LL_STREAM_U8) {
+    if (int r = make_plan_i8(N, K, group, nmat, grid, true, &pl)) return r;
+  } else if (int r = make_plan(N, K, group, nmat, M, grid, true, &pl)) return r;
   if (smem_bytes) *smem_bytes = pl.smem;
   if (ctas) *ctas = pl.P;
   return LL_OK;
@@ -951,7 +1562,12 @@ int ll_int4_gemv(const ll_gemv_args* a, ll_stream stream) {
   }
   cudaStream_t st = (cudaStream_t)stream;
   Plan pl;
-  if (int r = make_plan(a->N, a->K, a->group, nmat, a->M, a->grid, a->norm_weight != nullptr, &pl)) return r;
+  const bool i8 = a->stream_kind == LL_STREAM_U8;
+  LL_CHECK_ARG(a->stream_kind == LL_STREAM_BF16 || i8, "bad stream kind %d", a->stream_kind);
+  if (i8) {
+    LL_CHECK_ARG(a->M == 1 && a->epilogue != LL_EPI_PUSH, "stream kind 1 serves batch 1 with the store / residual / RoPE / SwiGLU epilogues");
+    if (int r = make_plan_i8(a->N, a->K, a->group, nmat, a->grid, a->norm_weight != nullptr, &pl)) return r;
+  } else if (int r = make_plan(a->N, a->K, a->group, nmat, a->M, a->grid, a->norm_weight != nullptr, &pl)) return r;
 
   Params p;
   memset(&p, 0, sizeof(p));
@@ -987,7 +1603,7 @@ int ll_int4_gemv(const ll_gemv_args* a, ll_stream stream) {
     delay_ns = e ? atoi(e) : 0;
   }
   p.prefetch_delay_ns = pdl ? delay_ns : 0;
-  return launch_plan(p, pl, pdl, st);
+  return i8 ? launch_plan_i8(p, pl, pdl, st) : launch_plan(p, pl, pdl, st);
 }
 
 }  // extern "C"

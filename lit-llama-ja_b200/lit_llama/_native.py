@@ -43,6 +43,7 @@ class GemvArgs(C.Structure):
         ("n_head", C.c_int32), ("head_size", C.c_int32), ("cache_len", C.c_int32),
         ("grid", C.c_int32),
         ("push_dst", C.c_uint64 * 8), ("push_cnt", C.c_uint64 * 8), ("push_world", C.c_int32),
+        ("stream_kind", C.c_int32),
     ]
 
 
@@ -62,7 +63,8 @@ EXPORTS = {
     "ll_get_weight": ([vp, vp, vp, i32, vp, i32, i32, i32, i32, i32, vp], C.c_int),
     "ll_qlinear_simt": ([vp, i32, i32, vp, vp, vp, i32, vp, vp, i32, i32, i32, i32, vp], C.c_int),
     "ll_int4_stream_bytes": ([i32, i32, i32], sz_t),
-    "ll_int4_prepare": ([vp, vp, vp, i32, vp, i32, i32, i32, vp, vp], C.c_int),
+    "ll_int4_prepare": ([vp, vp, vp, i32, vp, i32, i32, i32, i32, vp, vp], C.c_int),
+    "ll_int4_stream_kind": ([i32, i32, i32, i32], C.c_int),
     "ll_int4_gemv_plan": ([i32, i32, i32, i32, i32, i32, C.POINTER(sz_t), C.POINTER(C.c_int32)], C.c_int),
     "ll_int4_gemv": ([C.POINTER(GemvArgs), vp], C.c_int),
     "ll_gemm_bf16_tc": ([vp, vp, vp, vp, i32, i32, i32, vp], C.c_int),
@@ -142,6 +144,14 @@ def gemv_plan(N: int, K: int, group: int, nmat: int, M: int, grid: int = 0):
 
 def gemv_supported(N: int, K: int, group: int, nmat: int, M: int) -> bool:
     return _fn["ll_int4_gemv_plan"](N, K, group, nmat, M, 0, None, None) == 0
+
+
+STREAM_BF16, STREAM_U8 = 0, 1
+
+
+def stream_kind(N: int, K: int, group: int, M: int) -> int:
+    """The weight-stream kind the int4 GEMV wants for this shape and batch (LL_STREAM_*)."""
+    return _fn["ll_int4_stream_kind"](N, K, group, M)
 
 
 def stream_bytes(N: int, K: int, group: int) -> int:

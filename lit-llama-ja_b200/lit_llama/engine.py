@@ -57,7 +57,7 @@ class DecodeEngine:
         for lin in lins:
             if not isinstance(lin, ColBlockQuantizedLinear) or lin.bias is not None:
                 return False
-            if lin.scales.dtype != torch.bfloat16 or lin.prepare() is None:
+            if lin.scales.dtype != torch.bfloat16 or lin.prepare(B) is None:
                 return False
         for blk in model.transformer.h:
             if blk.mlp.c_fc1.tile_cols != blk.mlp.c_fc2.tile_cols:
@@ -128,9 +128,12 @@ class DecodeEngine:
     # ------------------------------------------------------------------ argument blocks
     def _gemv_args(self, lin, x, y, epi, plan, norm=None, lin2=None):
         a = N.GemvArgs()
-        a.w = lin._stream.data_ptr()
+        w, a.stream_kind = lin.stream_for(self.B)
+        if epi == N.EPI_PUSH and a.stream_kind != N.STREAM_BF16:
+            raise RuntimeError("the push exchange needs the bf16 weight stream: run with LLB200_GEMV_KIND=0")
+        a.w = w.data_ptr()
         if lin2 is not None:
-            a.w2 = lin2._stream.data_ptr()
+            a.w2 = lin2.stream_for(self.B)[0].data_ptr()
         a.N, a.K, a.group, a.M = lin.out_features, lin.in_features, lin.tile_cols, self.B
         a.x, a.y = x.data_ptr(), (y.data_ptr() if y is not None else 0)
         if norm is not None:

@@ -43,9 +43,7 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         self.register_buffer("zeros", torch.empty((out_features, n_groups)))
         assert isinstance(bias, bool)
         self.register_buffer("bias", torch.empty((out_features,)) if bias else None)
-        self._stream = None    # fragment-ordered repack of quant_weight/scales/zeros for the int4 GEMV (lazy)
-        self._stream_key = None
-        self._stream_ok = False
+        self._streams = {}     # stream kind -> (key, buffer, ok): fragment-ordered repacks of quant_weight/scales/zeros (lazy)
 
     # -- state-dict: accept a checkpoint whose group count differs from the constructor's
     # (``quantization("gptq.int4")`` always builds per-row modules, ref utils.py:179-191; a
@@ -59,7 +57,7 @@ class ColBlockQuantizedLinear(torch.nn.Module):
                 self.scales = torch.empty((self.out_features, g), dtype=self.scales.dtype, device=self.scales.device)
                 self.zeros = torch.empty_like(self.scales)
         super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)
-        self._stream = None
+        self._streams = {}
 
     def _apply(self, fn, *args, **kwargs):
         # keep the reference's (1, out) strides of quant_weight across .to()/.cuda()
@@ -67,7 +65,7 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         super()._apply(fn, *args, **kwargs)
         if stride_ok and self.quant_weight.stride() != (1, self.out_features):
             self.quant_weight = self.quant_weight.t().contiguous().t()
-        self._stream = None
+        self._streams = {}
         return self
 
     def _packed_ptr_ok(self):
@@ -87,7 +85,7 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         N.call("ll_pack_weight", N.ptr(weight), N.dtype_code(weight.dtype), N.ptr(self.scales.contiguous()),
                N.ptr(self.zeros.contiguous()), N.dtype_code(self.scales.dtype), N.ptr(qw), self.out_features,
                self.in_features, self.bits, self.tile_cols, N.stream())
-        self._stream = None
+        self._streams = {}
 
     def get_weight(self, dtype=torch.float):
         """ref: quantization.py:390-409 - bit-exact de-quantisation to ``[out, in]`` in ``dtype``."""
@@ -104,31 +102,39 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         return (self.bits == 4 and self.scales.dtype == self.zeros.dtype
                 and N.stream_bytes(self.out_features, self.in_features, self.tile_cols) > 0)
 
-    def prepare(self):
-        """Build (once) the fragment-ordered weight stream the int4 GEMV reads (a derived cache of
-        ``quant_weight``/``scales``/``zeros``; the checkpoint-layout buffers stay the state).
-        Returns it, or ``None`` when the layer cannot take the tensor-core GEMV (shape, or
-        scales / zeros not exactly representable in bf16)."""
-        key = (self.quant_weight.data_ptr(), self.scales.data_ptr(), self.zeros.data_ptr(),
-               self.quant_weight._version, self.scales._version, self.zeros._version)
-        if self._stream_key == key and self._stream is not None:
-            return self._stream if self._stream_ok else None
-        self._stream_key = key
+    def _state_key(self):
+        return (self.quant_weight.data_ptr(), self.scales.data_ptr(), self.zeros.data_ptr(),
+                self.quant_weight._version, self.scales._version, self.zeros._version)
+
+    def prepare(self, M: int = 1):
+        """Build (once per stream kind) the fragment-ordered weight stream the int4 GEMV reads at batch ``M`` (a derived
+        cache of ``quant_weight``/``scales``/``zeros``; the checkpoint-layout buffers stay the state): batch 1 with
+        128-multiple scale groups takes the integer-MMA kernel's layout, everything else the bf16 kernel's
+        (``ll_int4_stream_kind``).  Returns the stream, or ``None`` when the layer cannot take the tensor-core GEMV
+        (shape, or scales / zeros not exactly representable in bf16)."""
         if not self._fast_eligible():
-            self._stream, self._stream_ok = torch.empty(0), False
             return None
+        kind = N.stream_kind(self.out_features, self.in_features, self.tile_cols, M)
+        ent = self._streams.get(kind)
+        if ent is not None and ent[0] == self._state_key():
+            return ent[1] if ent[2] else None
         qw = self._packed_ptr_ok()
         dev = self.scales.device
         nbytes = N.stream_bytes(self.out_features, self.in_features, self.tile_cols)
         buf = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         status = torch.zeros(1, dtype=torch.int32, device=dev)
         N.call("ll_int4_prepare", N.ptr(qw), N.ptr(self.scales.contiguous()), N.ptr(self.zeros.contiguous()),
-               N.dtype_code(self.scales.dtype), N.ptr(buf), self.out_features, self.in_features, self.tile_cols,
+               N.dtype_code(self.scales.dtype), N.ptr(buf), self.out_features, self.in_features, self.tile_cols, kind,
                N.ptr(status), N.stream())
-        self._stream, self._stream_ok = buf, int(status.item()) == 0
-        self._stream_key = (self.quant_weight.data_ptr(), self.scales.data_ptr(), self.zeros.data_ptr(),
-                            self.quant_weight._version, self.scales._version, self.zeros._version)
-        return self._stream if self._stream_ok else None
+        ok = int(status.item()) == 0
+        self._streams[kind] = (self._state_key(), buf, ok)
+        return buf if ok else None
+
+    def stream_for(self, M: int):
+        """(prepared stream, its kind) for batch ``M`` WITHOUT building it (safe under CUDA-graph capture), or (None, kind)."""
+        kind = N.stream_kind(self.out_features, self.in_features, self.tile_cols, M)
+        ent = self._streams.get(kind)
+        return ((ent[1] if ent is not None and ent[2] else None), kind)
 
     # ------------------------------------------------------------------ row F
     def forward(self, inp):
@@ -149,9 +155,9 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         y = torch.empty((M, Nout), device=inp.device, dtype=inp.dtype)
         fast = inp.dtype == torch.bfloat16 and M <= 8 and N.gemv_supported(Nout, K, self.tile_cols, 1, M)
         if fast and torch.cuda.is_current_stream_capturing():
-            fast = self._stream is not None and self._stream_ok   # the stream must have been prepared before capture
+            fast = self.stream_for(M)[0] is not None   # the stream must have been prepared before capture
         elif fast:
-            fast = self.prepare() is not None
+            fast = self.prepare(M) is not None
         if fast:
             self._gemv(x, y)
         elif M <= 16:
@@ -165,7 +171,8 @@ class ColBlockQuantizedLinear(torch.nn.Module):
 
     def _gemv(self, x, y, *, pdl=False, grid=0):
         a = N.GemvArgs()
-        a.w = self._stream.data_ptr()
+        w, a.stream_kind = self.stream_for(x.shape[0])
+        a.w = w.data_ptr()
         a.N, a.K, a.group, a.M = self.out_features, self.in_features, self.tile_cols, x.shape[0]
         a.x, a.y = x.data_ptr(), y.data_ptr()
         a.bias = 0 if self.bias is None else self.bias.data_ptr()
@@ -198,8 +205,7 @@ def qlinear_4bit_weight(inp, weight, scales, zeros):
     torch.nn.Module.__init__(lin)
     lin.in_features, lin.out_features, lin.bits, lin.entries_per_byte, lin.tile_cols = K, weight.shape[0], 4, 2, K
     lin.quant_weight, lin.scales, lin.zeros, lin.bias = weight, scales, zeros, None
-    lin._stream = lin._stream_key = None
-    lin._stream_ok = False
+    lin._streams = {}
     return lin(inp)
 
 

@@ -5,6 +5,7 @@
 // sub-partition; a main loop that is to catch up after a kernel boundary wants <= 16.
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o loop_mix loop_mix.cu ; ./loop_mix
 #include <cstdio>
+#include <cstdlib>
 #include <cstdint>
 #include <cuda_runtime.h>
 
@@ -171,6 +172,10 @@ __global__ void rate_kernel(float* out, long long* cycles, int iters) {
       else if (KIND == 7) asm volatile("lop3.b32 %0, %0, %1, %2, 0xea;" : "+r"(r[i]) : "r"(b), "r"(0x41804180u));
       else if (KIND == 8) asm volatile("fma.rn.f32 %0, %1, %2, %0;" : "+f"(c[i]) : "f"(__uint_as_float(r[i])), "f"(__uint_as_float(b)));
       else if (KIND == 9) asm volatile("sub.bf16x2 %0, %0, %1;" : "+r"(r[i]) : "r"(b));
+      else if (KIND == 10) asm volatile("cvt.rni.s32.f32 %0, %1;" : "=r"(r[i]) : "f"(c[i] + __uint_as_float(r[i])));
+      else if (KIND == 11) asm volatile("cvt.rn.f32.s32 %0, %1;" : "=f"(c[i]) : "r"(r[i]));
+      else if (KIND == 12) asm volatile("max.bf16x2 %0, %0, %1;" : "+r"(r[i]) : "r"(b));
+      else if (KIND == 13) asm volatile("mul.rn.bf16x2 %0, %0, %1;" : "+r"(r[i]) : "r"(b));
     }
   }
   long long t1 = clock64();
@@ -225,6 +230,11 @@ int main() {
   run_rate<2>("SHF");
   run_rate<7>("LOP3");
   run_rate<5>("PRMT");
+  run_rate<10>("F2I (+1 FADD)");
+  run_rate<11>("I2F");
+  run_rate<12>("HMNMX2.BF16");
+  run_rate<13>("HMUL2.BF16");
+  if (getenv("RATES_ONLY")) return 0;
   run_mix<0>("today: LDS w + LDS x frags + 7 ALU + HMMA");
   run_mix<1>("x-stationary: 7 ALU + HMMA");
   run_mix<4>("x-stationary fp16: 5 ALU + HMMA");

@@ -275,7 +275,7 @@ def _bf16_layer(N_, K, group, seed):
     return OQ.pack_weight(Q, s, z, 4, group, "bf16"), s, z
 
 
-def _stream_of(packed, s, z, N_, K, group):
+def _stream_of(packed, s, z, N_, K, group, M=1):
     from lit_llama.quantization import ColBlockQuantizedLinear
 
     torch.set_default_dtype(torch.bfloat16)
@@ -286,7 +286,7 @@ def _stream_of(packed, s, z, N_, K, group):
     lin = lin.to(DEV)
     lin.scales.copy_(torch.from_numpy(s)); lin.zeros.copy_(torch.from_numpy(z))
     lin.quant_weight.copy_(torch.from_numpy(packed))
-    assert lin.prepare() is not None
+    assert lin.prepare(M) is not None
     return lin
 
 
@@ -322,9 +322,10 @@ def test_specialised_gemv_epilogues_with_fused_norm_at_7b_shapes(M):
 
     def gemv(lin, x, y, epi, norm_w=None, lin2=None, **kw):
         a = NV.GemvArgs()
-        a.w = lin._stream.data_ptr()
+        w, a.stream_kind = lin.stream_for(M)
+        a.w = w.data_ptr()
         if lin2 is not None:
-            a.w2 = lin2._stream.data_ptr()
+            a.w2 = lin2.stream_for(M)[0].data_ptr()
         a.N, a.K, a.group, a.M = lin.out_features, lin.in_features, group, M
         a.x, a.y = x.data_ptr(), y.data_ptr()
         if norm_w is not None:
@@ -345,7 +346,7 @@ def test_specialised_gemv_epilogues_with_fused_norm_at_7b_shapes(M):
 
     # ---- lm_head: fused norm + store
     pk, s, z = _bf16_layer(V, E, group, 21)
-    lin = _stream_of(pk, s, z, V, E, group)
+    lin = _stream_of(pk, s, z, V, E, group, M)
     y = torch.empty((M, V), device=DEV, dtype=torch.bfloat16)
     gemv(lin, dev(xraw), y, NV.EPI_STORE, norm_w=dev(nw))
     close(y.float().cpu().numpy(), _exact(xn, pk, s, z, group), _mag(xn, pk, s, z, group))
@@ -353,7 +354,7 @@ def test_specialised_gemv_epilogues_with_fused_norm_at_7b_shapes(M):
     # ---- fc1|fc2: fused norm + SwiGLU
     pk1, s1, z1 = _bf16_layer(H, E, group, 22)
     pk2, s2, z2 = _bf16_layer(H, E, group, 23)
-    l1, l2 = _stream_of(pk1, s1, z1, H, E, group), _stream_of(pk2, s2, z2, H, E, group)
+    l1, l2 = _stream_of(pk1, s1, z1, H, E, group, M), _stream_of(pk2, s2, z2, H, E, group, M)
     y = torch.empty((M, H), device=DEV, dtype=torch.bfloat16)
     gemv(l1, dev(xraw), y, NV.EPI_SWIGLU, norm_w=dev(nw), lin2=l2)
     a, b = bf(_exact(xn, pk1, s1, z1, group)), bf(_exact(xn, pk2, s2, z2, group))
@@ -365,7 +366,7 @@ def test_specialised_gemv_epilogues_with_fused_norm_at_7b_shapes(M):
 
     # ---- mlp.c_proj: K = 11008, residual add in place
     pk, s, z = _bf16_layer(E, H, group, 24)
-    lin = _stream_of(pk, s, z, E, H, group)
+    lin = _stream_of(pk, s, z, E, H, group, M)
     h = bf(r.randn(M, H))
     res = bf(r.randn(M, E))
     y = dev(res)
@@ -377,7 +378,7 @@ def test_specialised_gemv_epilogues_with_fused_norm_at_7b_shapes(M):
 
     # ---- attn.c_proj: K = 4096, residual
     pk, s, z = _bf16_layer(E, E, group, 25)
-    lin = _stream_of(pk, s, z, E, E, group)
+    lin = _stream_of(pk, s, z, E, E, group, M)
     att = bf(r.randn(M, E))
     y = dev(res)
     gemv(lin, dev(att), y, NV.EPI_RESIDUAL)
@@ -388,7 +389,7 @@ def test_specialised_gemv_epilogues_with_fused_norm_at_7b_shapes(M):
 
     # ---- c_attn: fused norm + RoPE (interleaved pairs, ref model.py:312-329) + KV write at the ring slot
     pk, s, z = _bf16_layer(3 * E, E, group, 26)
-    lin = _stream_of(pk, s, z, 3 * E, E, group)
+    lin = _stream_of(pk, s, z, 3 * E, E, group, M)
     pos, slot = 37, 5
     rope = OM.build_rope_cache(64, hs)
     q = torch.zeros((M, E), device=DEV, dtype=torch.bfloat16)

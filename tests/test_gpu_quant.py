@@ -60,7 +60,7 @@ def test_pack_unpack_bit_exact_vs_reference_golden(golden, dt):
         ref = g[f"{name}.{dt}.forward"]
         if dt == "fp32":
             np.testing.assert_allclose(y, ref, rtol=1e-5, atol=1e-6)
-        elif bits == 4 and lin.prepare() is not None:
+        elif bits == 4 and lin.prepare(g[f"{name}.x"].reshape(-1, g[f"{name}.x"].shape[-1]).shape[0]) is not None:
             # streamed GEMV: exact dequant (no bf16 rounding of the weights) - bf16 tolerance vs the reference
             assert np.abs(y - ref).max() <= 0.02 * np.abs(ref).max(), name
         else:
@@ -140,15 +140,51 @@ def stream_decode(buf, N, K, group):
     return codes, sc, zr
 
 
+def stream_decode_u8(buf, N, K, group):
+    """Host-side inverse of the kind-1 repack (LL_STREAM_U8, include/llb200.h): the lane's word 4 q + j of a block holds
+    k = 32 tig + 4 (4 q + j) + i in byte i: column g in the low nibble, column g + 8 in the high nibble; tail (scale, -zero)."""
+    KB = 128
+    G, BLK = K // KB, KB * 8 + 64
+    blocks = np.frombuffer(buf.tobytes(), dtype=np.uint8).reshape(N // 16, G, BLK)
+    words = blocks[:, :, :KB * 8].copy().view(np.uint32).reshape(N // 16, G, KB * 2)
+    tail = blocks[:, :, KB * 8:].copy().view(np.uint32).reshape(N // 16, G, 16)
+    codes = np.zeros((N, K), np.uint8)
+    r = np.arange(KB * 2)
+    q, lane, j = r >> 7, (r & 127) >> 2, r & 3
+    g, tig = lane >> 2, lane & 3
+    kin = 32 * tig + 4 * (4 * q + j)
+    for i in range(4):
+        lo = ((words >> np.uint32(8 * i)) & np.uint32(15)).astype(np.uint8)
+        hi = ((words >> np.uint32(8 * i + 4)) & np.uint32(15)).astype(np.uint8)
+        for t in range(N // 16):
+            for gk in range(G):
+                codes[t * 16 + g, gk * KB + kin + i] = lo[t, gk]
+                codes[t * 16 + g + 8, gk * KB + kin + i] = hi[t, gk]
+    e = np.arange(16)
+    ncol = (e >> 1) + 8 * (e & 1)
+    sc = np.zeros((N, G), np.float32)
+    zr = np.zeros((N, G), np.float32)
+    for t in range(N // 16):
+        sc[t * 16 + ncol] = OQ.from_bf16_bits((tail[t] & 0xffff).astype(np.uint16)).T
+        zr[t * 16 + ncol] = (-OQ.from_bf16_bits((tail[t] >> 16).astype(np.uint16))).T
+    return codes, sc, zr
+
+
+@pytest.mark.parametrize("M", [1, 2])
 @pytest.mark.parametrize("N,K,tile", [(48, 256, 128), (32, 128, 32), (64, 192, 64), (16, 512, -1), (4096, 4096, 128)])
-def test_int4_stream_repack_is_bit_exact_reindexing(N, K, tile):
-    """Every nibble of the checkpoint bytes lands at its documented stream position; scales exact; zero exact."""
+def test_int4_stream_repack_is_bit_exact_reindexing(N, K, tile, M):
+    """Every nibble of the checkpoint bytes lands at its documented stream position; scales exact; zero exact - for both
+    stream kinds (batch 1 with 128-multiple groups takes the integer-MMA layout, everything else the bf16 one)."""
+    from lit_llama import _native as NV
+
     packed, s, z = _bf16_layer(N, K, tile, N + K)
     lin = make_lin(N, K, 4, tile, s, z, "bf16", packed)
-    st = lin.prepare()
+    st = lin.prepare(M)
     assert st is not None
     group = K if tile == -1 else tile
-    codes, sc, zr = stream_decode(st.cpu().numpy(), N, K, group)
+    kind = NV.stream_kind(N, K, group, M)
+    assert kind == (NV.STREAM_U8 if (M == 1 and group % 128 == 0 and (K // 128) % 2 == 0) else NV.STREAM_BF16)
+    codes, sc, zr = (stream_decode_u8 if kind == NV.STREAM_U8 else stream_decode)(st.cpu().numpy(), N, K, group)
     assert np.array_equal(codes, OQ.unpack_codes(packed, 4))
     KB = 128 if group % 128 == 0 else (64 if group % 64 == 0 else 32)
     rep = group // KB
@@ -166,7 +202,7 @@ def test_int4_gemv_vs_oracle(N, K, tile, M):
     the reference's fallback numerics (get_weight(bf16) + matmul)."""
     packed, s, z = _bf16_layer(N, K, tile, N + K + M)
     lin = make_lin(N, K, 4, tile, s, z, "bf16", packed)
-    assert lin.prepare() is not None
+    assert lin.prepare(M) is not None
     x = OQ.bf16_round(np.random.RandomState(1).randn(M, K).astype(np.float32))
     y = lin(torch.from_numpy(x).to(DEV, torch.bfloat16)).float().cpu().numpy()
     exact_close(y, x, packed, s, z, tile)
@@ -177,17 +213,18 @@ def test_int4_gemv_vs_oracle(N, K, tile, M):
     assert np.array_equal(y, y2)
 
 
-def test_int4_gemv_forced_grid_matches():
-    """Any CTA count gives the same bits: a tile is summed inside one CTA in a fixed order."""
+@pytest.mark.parametrize("M", [1, 2])
+def test_int4_gemv_forced_grid_matches(M):
+    """Any CTA count gives the same bits: a tile is summed inside one CTA in a fixed order (both kernels)."""
     N_, K, tile = 512, 2048, 128
     packed, s, z = _bf16_layer(N_, K, tile, 5)
     lin = make_lin(N_, K, 4, tile, s, z, "bf16", packed)
-    lin.prepare()
-    xn = OQ.bf16_round(np.random.RandomState(2).randn(2, K).astype(np.float32))
+    lin.prepare(M)
+    xn = OQ.bf16_round(np.random.RandomState(2).randn(M, K).astype(np.float32))
     x = torch.from_numpy(xn).to(DEV, torch.bfloat16)
     outs = []
     for grid in (1, 2, 3, 7, 32, 100, 148, 512):
-        y = torch.empty((2, N_), device=DEV, dtype=torch.bfloat16)
+        y = torch.empty((M, N_), device=DEV, dtype=torch.bfloat16)
         lin._gemv(x, y, grid=grid)
         outs.append(y.float().cpu().numpy())
         exact_close(outs[-1], xn, packed, s, z, tile)
@@ -219,10 +256,15 @@ def test_non_integer_zero_falls_back_to_simt():
     z = z + 0.3
     z = OQ.bf16_round(z)
     lin = make_lin(128, 256, 4, 128, s, z, "bf16", packed)
-    assert lin.prepare() is None
-    x = OQ.bf16_round(np.random.RandomState(1).randn(1, 256).astype(np.float32))
+    # the bf16 kernel needs -(16 + zero) exact in bf16: not so here -> reference-semantics SIMT kernel at batch 2
+    assert lin.prepare(2) is None
+    x = OQ.bf16_round(np.random.RandomState(1).randn(2, 256).astype(np.float32))
     y = lin(torch.from_numpy(x).to(DEV, torch.bfloat16)).float().cpu().numpy()
     ulp_close(y, OQ.linear_forward(x, packed, s, z, None, 4, 128, "bf16"))   # SIMT path: reference rounding steps
+    # the batch-1 integer kernel carries any bf16 zero exactly (sum q x - zero sum x)
+    assert lin.prepare(1) is not None
+    y1 = lin(torch.from_numpy(x[:1]).to(DEV, torch.bfloat16)).float().cpu().numpy()
+    exact_close(y1, x[:1], packed, s, z, 128)
 
 
 def test_errors_are_loud():
