@@ -355,7 +355,8 @@ def main():
             out.update(kernel_metrics(model, device))
             if os.environ.get("LLB200_BENCH_REFGPU", "1") != "0":
                 out["reference_gpu"] = reference_gpu(model, device)
-            out["cpu_baseline"] = cpu_baseline(prefill_sample=64, decode_tokens=1)
+            if os.environ.get("LLB200_BENCH_CPU", "1") != "0":     # (profiling runs skip the host leg)
+                out["cpu_baseline"] = cpu_baseline(prefill_sample=64, decode_tokens=1)
     else:
         out["comm"] = {"collective": "tp_allreduce_add_kernel (peer pull over NVLink, in the step's CUDA graph)",
                        "exchanges_per_token": 2 * model.config.n_layer, "bytes_per_exchange": model.config.n_embd * 2,

@@ -160,6 +160,18 @@ LL_API int ll_int4_gemv(const ll_gemv_args* args /* host */, ll_stream stream);
  * ------------------------------------------------------------------------------------- */
 LL_API int ll_gemm_bf16_tc(const void* x, const void* w, const void* bias, void* y, int M, int N, int K, ll_stream stream);
 
+/* Fused int4 de-quantise + GEMM on tcgen05 for 1 <= M <= 128 rows (batched decode, short prefill; the HBM-bound regime):
+ * y[M][N] (bf16) = x[M][K] (bf16) . W^T (+ bias), W de-quantised INSIDE the main loop from the packed stream
+ * (w_stream = ll_int4_prepare(..., LL_STREAM_U8, ...), the batch-1 GEMV's stream) with the reference's bf16 rounding steps
+ * bf16(bf16(q - zero) * scale) (get_weight, ref quantization.py:390-409), fp32 accumulation in tensor memory - the
+ * arithmetic of F.linear(inp, get_weight(bf16)) (ref quantization.py:420-421) and the structure of the reference's
+ * Triton kernel (de-quantise in the K loop, ref quantization.py:259-267).  N % 128 == 0, group % 128 == 0, K % group == 0.
+ * K is split over CTAs to fill the SMs; `scratch` (ll_int4_gemm_tc_scratch_bytes(), may be 0 -> NULL allowed) holds the
+ * partial sums, added in a fixed order by a second kernel. */
+LL_API size_t ll_int4_gemm_tc_scratch_bytes(int M, int N, int K);
+LL_API int ll_int4_gemm_tc(const uint8_t* w_stream, const void* x, const void* bias, void* y, float* scratch, int M, int N,
+                           int K, int group, ll_stream stream);
+
 /* ---------------------------------------------------------------------------------------
  * llm.int8 (ref: Linear8bitLt, quantization.py:36-75; arithmetic = bitsandbytes double_quant / MatMul8bitLt,
  * un-vendored in the reference, restated from arXiv:2208.07339 - see oracle/quant.py).

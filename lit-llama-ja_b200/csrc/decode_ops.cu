@@ -139,7 +139,20 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
                                                           const T* __restrict__ vc, const int32_t* __restrict__ pos,
                                                           T* __restrict__ y, int n_head, int S, int nsplit,
                                                           float* __restrict__ scratch, int32_t* __restrict__ counters,
-                                                          int use_pdl) {
+                                                          int use_pdl, unsigned long long* __restrict__ trace) {
+#ifdef LLB_TRACE  // tuning build: %globaltimer stamps per CTA (profiles/attn_trace.py)
+#define ATRACE(i)                                                                                     \
+  do {                                                                                                \
+    if (trace != nullptr && threadIdx.x == 0) {                                                       \
+      unsigned long long t_;                                                                          \
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_));                                           \
+      trace[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 4 + (i)] = t_;                            \
+    }                                                                                                 \
+  } while (0)
+#else
+#define ATRACE(i) do { } while (0)
+#endif
+  ATRACE(0);
   constexpr int EPL = HS / 8;
   constexpr int NW = 4;
   __shared__ float s_m[NW * 4], s_l[NW * 4];
@@ -153,6 +166,7 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
   const int trig = use_pdl >> 1;
   if (trig == 1 || (use_pdl & 1)) pdl_launch_dependents();
   if (use_pdl & 1) pdl_wait();
+  ATRACE(1);
   const int bh = blockIdx.x, split = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, lg = lane >> 3, li = lane & 7;
   const int nvalid = min(pos[2], S);
@@ -201,6 +215,7 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
     }
   }
   if (trig == 2) pdl_launch_dependents();
+  ATRACE(2);
   // combine the 16 (warp, lane-group) partial states of this CTA in fixed order
   if (li == 0) { s_m[warp * 4 + lg] = m; s_l[warp * 4 + lg] = l; }
 #pragma unroll
@@ -240,6 +255,7 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
     if (nsplit > 1) {
       asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
       asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+      ATRACE(3);
       if (split != 0) return;
       if (threadIdx.x < HS) {
         float M = -INFINITY;
@@ -385,6 +401,13 @@ size_t ll_decode_attn_scratch_bytes(int B, int n_head, int head_size, int max_sp
   return (size_t)B * n_head * max_splits * (head_size + 2) * sizeof(float);
 }
 
+unsigned long long* g_attn_trace = nullptr;  // debug: device buffer [launches][CTAs <= 512][4]
+int g_attn_trace_launches = 0, g_attn_trace_idx = 0;
+/* debug (not in the public header): stamp the next `launches` decode-attention launches */
+__attribute__((visibility("default"))) void ll_debug_attn_trace(unsigned long long* buf, int launches) {
+  g_attn_trace = buf; g_attn_trace_launches = launches; g_attn_trace_idx = 0;
+}
+
 int ll_decode_attn(const void* q, const void* k_cache, const void* v_cache, const int32_t* pos, void* y, int dtype, int B,
                    int n_head, int head_size, int cache_len, int max_splits, float* scratch, int32_t* counters,
                    int flags, ll_stream stream) {
@@ -407,6 +430,9 @@ int ll_decode_attn(const void* q, const void* k_cache, const void* v_cache, cons
     if (trig < 0 || trig > 2) trig = 0;
   }
   const int kflags = (pdl ? 1 : 0) | (trig << 1);
+  unsigned long long* tr = nullptr;
+  if (g_attn_trace != nullptr && g_attn_trace_idx < g_attn_trace_launches && grid.x * grid.y <= 512)
+    tr = g_attn_trace + (size_t)(g_attn_trace_idx++) * 512 * 4;
   const bool cl = use_cluster && max_splits >= 2 && max_splits <= 8;
 #define ATTN(TT, HS)                                                                                              \
   do {                                                                                                            \
@@ -427,10 +453,10 @@ int ll_decode_attn(const void* q, const void* k_cache, const void* v_cache, cons
       cfg.attrs = attr; cfg.numAttrs = pdl ? 2 : 1;                                                               \
       LL_CUDA(cudaLaunchKernelEx(&cfg, decode_attn_kernel<TT, HS, true>, (const TT*)q, (const TT*)k_cache,        \
                                  (const TT*)v_cache, pos, (TT*)y, n_head, cache_len, max_splits, scratch, counters, \
-                                 kflags));                                                                   \
+                                 kflags, tr));                                                                 \
     } else {                                                                                                      \
       LL_CUDA(launch(decode_attn_kernel<TT, HS, false>, grid, block, 0, st, pdl, (const TT*)q, (const TT*)k_cache, \
-                     (const TT*)v_cache, pos, (TT*)y, n_head, cache_len, max_splits, scratch, counters, kflags)); \
+                     (const TT*)v_cache, pos, (TT*)y, n_head, cache_len, max_splits, scratch, counters, kflags, tr)); \
     }                                                                                                             \
   } while (0)
   if (dtype == LL_BF16) {

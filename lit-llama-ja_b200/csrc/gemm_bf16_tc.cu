@@ -270,6 +270,291 @@ int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* C, 
   return LL_OK;
 }
 
+// ==================================================================================== fused int4 dequant-GEMM, M <= 128
+// y[M][N] = x[M][K] . dequant(W)^T for 9 <= M <= 128 (batched decode, short prefill): the regime where the weights are
+// the traffic (HBM-bound), so they are streamed ONCE in their packed form and de-quantised inside the main loop - what the
+// reference's Triton kernel does (ref quantization.py:259-267: load nibble, (q - zero) * scale, tl.dot) - instead of
+// writing a bf16 copy of W to HBM and reading it back.  (For M in the thousands the same idea is counter-productive on
+// this machine: the tensor cores consume a 128-row tile's weights in K/16 * ~8 clk while de-quantising them costs
+// ~0.06 clk per weight of ALU time per SM, so every 128-row block of M would pay the de-quantisation again; there the
+// two-pass path above is within 3 % of the GEMM alone.  DESIGN.md section 3.)
+//
+//  * operand roles are swapped: the WEIGHTS are the A operand (128 output columns = the 128 TMEM lanes) and live in TENSOR
+//    MEMORY: each of 128 de-quantising threads owns one output column, reads its nibbles from the packed stream (kind 1,
+//    the batch-1 GEMV's stream: no second copy of the weights), forms bf16((q - zero) * scale) with the reference's two
+//    bf16 roundings (HSUB2.BF16 exact for integer zeros, HMUL2.BF16 rounded) and writes 16 k per tcgen05.st;
+//    the ACTIVATIONS are the B operand, TMA-loaded [M_pad][64 k] tiles (128-byte swizzle); D[128][M_pad] fp32 in TMEM.
+//  * one thread issues tcgen05.mma (128 x M_pad x 16, A from TMEM); A is double-buffered (2 x 64 columns) so that
+//    de-quantising k-block i + 1 overlaps the MMAs of block i; a 4-stage TMA ring feeds packed blocks and x tiles.
+//  * work unit = (128-column tile, k-range): K is split so that the units fill the SMs; partial sums go to a scratch
+//    buffer and a second small kernel adds them in split order (deterministic), adds the bias and rounds to bf16.
+constexpr int W4_BN = 128;          // output columns per unit = TMEM lanes
+constexpr int W4_KB = 128;          // k per block of the packed stream
+constexpr int W4_BLK = W4_KB * 8 + 64;
+constexpr int W4_STAGES = 4;
+
+__device__ __forceinline__ void umma_ts_bf16(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_x8(uint32_t taddr, const uint32_t (&r)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr), "r"(r[0]), "r"(r[1]),
+               "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+__device__ __forceinline__ uint32_t w4_prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+  return r;
+}
+__device__ __forceinline__ uint32_t w4_sub2(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("sub.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t w4_mul2(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ void w4_bulk_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+struct W4Params {
+  const uint8_t* w;       // stream kind 1: [N/16][K/128] blocks of 1088 B
+  __nv_bfloat16* y;       // [M][N] (written directly when ksplit == 1)
+  float* scratch;         // [tiles][ksplit][M_pad][128] partial sums (ksplit > 1)
+  const __nv_bfloat16* bias;
+  int M, N, K, G, ksplit, mpad;
+};
+
+template <int MPAD>
+__global__ void __launch_bounds__(192, 1) gemm_w4_tc_kernel(const __grid_constant__ CUtensorMap map_x, const W4Params p) {
+  constexpr int W_BYTES = 8 * W4_BLK;        // eight 16-column blocks of the stream = 128 columns x 128 k
+  constexpr int X_ATOM = MPAD * 128;         // [MPAD][64 k] bf16, swizzled
+  constexpr int X_BYTES = 2 * X_ATOM;
+  constexpr int STAGE = ((W_BYTES + 1023) / 1024) * 1024 + X_BYTES;
+  constexpr int X_OFF = ((W_BYTES + 1023) / 1024) * 1024;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full = reinterpret_cast<uint64_t*>(base + W4_STAGES * STAGE);
+  uint64_t* empty = full + W4_STAGES;
+  uint64_t* a_ready = empty + W4_STAGES;   // [2] A buffer written (4 warps)
+  uint64_t* a_free = a_ready + 2;          // [2] A buffer consumed (commit)
+  uint64_t* tmem_full = a_free + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tile = blockIdx.x / p.ksplit, ks = blockIdx.x - tile * p.ksplit;
+  const int kb0 = (int)(((long long)p.G * ks) / p.ksplit), kb1 = (int)(((long long)p.G * (ks + 1)) / p.ksplit);
+  const int nkb = kb1 - kb0;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&map_x);
+    for (int i = 0; i < W4_STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 5);  // 4 de-quantising warps + the MMA commit
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&a_ready[i], 4);
+      mbar_init(&a_free[i], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_ptr, 256);  // D: columns [0, MPAD); A buffers: [128, 192) and [192, 256)
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer: eight packed blocks + two x atoms per 128 k =====================
+    if (lane == 0) {
+      int s = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < nkb; ++i) {
+        const int kb = kb0 + i;
+        mbar_wait_parity(&empty[s], phase ^ 1);
+        mbar_expect_tx(&full[s], W_BYTES + X_BYTES);
+        uint8_t* st = base + s * STAGE;
+#pragma unroll
+        for (int t = 0; t < 8; ++t)
+          w4_bulk_1d(st + t * W4_BLK, p.w + ((size_t)(tile * 8 + t) * p.G + kb) * W4_BLK, W4_BLK, &full[s]);
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+          asm volatile(
+              "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                  smem_u32(st + X_OFF + a * X_ATOM)),
+              "l"(&map_x), "r"(kb * W4_KB + a * 64), "r"(0), "r"(smem_u32(&full[s]))
+              : "memory");
+        if (++s == W4_STAGES) {
+          s = 0;
+          phase ^= 1u;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = instr_desc_bf16(128, MPAD);
+      int s = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < nkb; ++i) {
+        const int buf = i & 1;
+        mbar_wait_parity(&full[s], phase);                   // the x atoms of this stage have landed
+        mbar_wait_parity(&a_ready[buf], (uint32_t)(i >> 1) & 1u);  // the weights of this block are in tensor memory
+        tc_fence_after();
+        const uint32_t xs = smem_u32(base + s * STAGE + X_OFF);
+        const uint32_t ta = tmem_base + 128u + (uint32_t)buf * 64u;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const uint64_t bdesc = smem_desc_sw128(xs + (uint32_t)(k >> 2) * X_ATOM) + (uint64_t)(2 * (k & 3));
+          umma_ts_bf16(tmem_base, ta + (uint32_t)(8 * k), bdesc, idesc, (i | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&a_free[buf]);
+        umma_commit(&empty[s]);
+        if (++s == W4_STAGES) {
+          s = 0;
+          phase ^= 1u;
+        }
+      }
+      umma_commit(tmem_full);
+    }
+  } else {
+    // ===================== de-quantising warps 2..5, then the epilogue =====================
+    const int quarter = warp & 3;            // a warp may only touch TMEM lanes [32 * (warpid % 4), +32)
+    const int t = quarter * 32 + lane;       // TMEM lane = output column n0 + t
+    const int t16 = t >> 4, g = t & 7, hi = (t >> 3) & 1;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    const uint32_t sh = 4u * (uint32_t)hi;
+    int s = 0;
+    uint32_t phase = 0;
+    for (int i = 0; i < nkb; ++i) {
+      const int buf = i & 1;
+      mbar_wait_parity(&full[s], phase);
+      if (i >= 2) mbar_wait_parity(&a_free[buf], (uint32_t)((i >> 1) - 1) & 1u);
+      tc_fence_after();
+      const uint32_t blk = smem_u32(base + s * STAGE + t16 * W4_BLK);
+      uint32_t sz;
+      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(sz) : "r"(blk + 1024u + (uint32_t)(2 * g + hi) * 4u));
+      const uint32_t s2 = (sz & 0xffffu) * 0x00010001u;  // bf16x2 (scale, scale)
+      const uint32_t z2 = ((sz >> 16) ^ 0x8000u) * 0x00010001u;  // tail holds -zero: bf16x2 (zero, zero)
+      const uint32_t ta = lane_addr + 128u + (uint32_t)buf * 64u;
+#pragma unroll
+      for (int m = 0; m < 8; ++m) {  // m = 2 tig + q: k = 32 tig + 16 q + 0..15 of the block -> TMEM columns 16 tig + 8 q + 0..7
+        const int tig = m >> 1, q = m & 1;
+        uint4 wq;
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wq.x), "=r"(wq.y), "=r"(wq.z), "=r"(wq.w)
+                     : "r"(blk + (uint32_t)(q * 512 + (g * 4 + tig) * 16)));
+        const uint32_t w[4] = {wq.x, wq.y, wq.z, wq.w};
+        uint32_t r[8];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t nib = (w[j] >> sh) & 0x0F0F0F0Fu;          // this column's four nibbles (k, k+1, k+2, k+3)
+          // bf16 (128 + q) = 0x4300 | q; minus 128, minus zero (both exact for integer zeros), times scale (rounded):
+          // the reference's get_weight in bf16 (quantization.py:399-408)
+          const uint32_t a = w4_sub2(w4_prmt(nib, 0x43434343u, 0x5140u), 0x43004300u);
+          const uint32_t b = w4_sub2(w4_prmt(nib, 0x43434343u, 0x5342u), 0x43004300u);
+          r[2 * j] = w4_mul2(w4_sub2(a, z2), s2);
+          r[2 * j + 1] = w4_mul2(w4_sub2(b, z2), s2);
+        }
+        tmem_st_x8(ta + (uint32_t)(16 * tig + 8 * q), r);
+      }
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&a_ready[buf]);
+        mbar_arrive(&empty[s]);
+      }
+      if (++s == W4_STAGES) {
+        s = 0;
+        phase ^= 1u;
+      }
+    }
+    // ---- epilogue: D[t][m] for m < M: thread t holds output column n0 + t
+    mbar_wait_parity(tmem_full, 0);
+    tc_fence_after();
+    const int n = tile * W4_BN + t;
+    const float bias = (p.bias != nullptr && p.ksplit == 1) ? __bfloat162float(p.bias[n]) : 0.f;
+#pragma unroll 1
+    for (int c0 = 0; c0 < MPAD; c0 += 16) {
+      uint32_t v[16];
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+            "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+          : "r"(lane_addr + (uint32_t)c0)
+          : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int m = c0 + j;
+        if (m < p.M) {
+          if (p.ksplit == 1) p.y[(size_t)m * p.N + n] = __float2bfloat16_rn(__uint_as_float(v[j]) + bias);
+          else p.scratch[(((size_t)tile * p.ksplit + ks) * MPAD + m) * W4_BN + t] = __uint_as_float(v[j]);
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 256);
+  }
+}
+
+// y[m][n] = bf16(sum over the k-splits, in split order, + bias)
+__global__ void w4_reduce_kernel(const float* __restrict__ scratch, const __nv_bfloat16* __restrict__ bias,
+                                 __nv_bfloat16* __restrict__ y, int M, int N, int ksplit, int mpad) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)M * N) return;
+  const int m = (int)(i / N), n = (int)(i - (size_t)m * N);
+  const int tile = n / W4_BN, t = n - tile * W4_BN;
+  float acc = 0.f;
+  for (int ks = 0; ks < ksplit; ++ks) acc += scratch[(((size_t)tile * ksplit + ks) * mpad + m) * W4_BN + t];
+  if (bias != nullptr) acc += __bfloat162float(bias[n]);
+  y[i] = __float2bfloat16_rn(acc);
+}
+
+template <int MPAD>
+int launch_w4(const CUtensorMap& mx, const W4Params& p, cudaStream_t st) {
+  constexpr size_t stage = ((8 * W4_BLK + 1023) / 1024) * 1024 + 2 * MPAD * 128;
+  constexpr size_t smem = W4_STAGES * stage + (2 * W4_STAGES + 5) * 8 + 16 + 1024;
+  static bool configured = false;
+  if (!configured) {
+    LL_CUDA(cudaFuncSetAttribute(gemm_w4_tc_kernel<MPAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  gemm_w4_tc_kernel<MPAD><<<(p.N / W4_BN) * p.ksplit, 192, smem, st>>>(mx, p);
+  LL_LAUNCH_OK("gemm_w4_tc_kernel");
+  return LL_OK;
+}
+
+// k-split that fills the SMs best (whole waves of one CTA per SM), each unit at least four k-blocks long
+int w4_pick_ksplit(int tiles, int G, int sms) {
+  int best = 1;
+  double best_eff = 0.0;
+  for (int ks = 1; ks <= 16 && G / ks >= 4; ++ks) {
+    const int units = tiles * ks;
+    const double eff = (double)units / ((double)((units + sms - 1) / sms) * sms);
+    if (eff > best_eff + 0.03) {
+      best_eff = eff;
+      best = ks;
+    }
+  }
+  return best;
+}
+
 }  // namespace
 }  // namespace llb
 
@@ -292,6 +577,46 @@ int ll_gemm_bf16_tc(const void* x, const void* w, const void* bias, void* y, int
   cudaStream_t st = (cudaStream_t)stream;
   if (wide) return launch_gemm<256, 4>(ma, mb, (__nv_bfloat16*)y, (const __nv_bfloat16*)bias, M, N, K, st);
   return launch_gemm<128, 6>(ma, mb, (__nv_bfloat16*)y, (const __nv_bfloat16*)bias, M, N, K, st);
+}
+
+size_t ll_int4_gemm_tc_scratch_bytes(int M, int N, int K) {
+  if (M <= 0 || N <= 0 || K <= 0 || N % W4_BN != 0 || K % W4_KB != 0) return 0;
+  const int mpad = M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : 128;
+  const int ks = w4_pick_ksplit(N / W4_BN, K / W4_KB, sm_count() > 0 ? sm_count() : 148);
+  return ks == 1 ? 0 : (size_t)(N / W4_BN) * ks * mpad * W4_BN * sizeof(float);
+}
+
+int ll_int4_gemm_tc(const uint8_t* w_stream, const void* x, const void* bias, void* y, float* scratch, int M, int N, int K,
+                    int group, ll_stream stream) {
+  LL_CHECK_ARG(w_stream && x && y, "null pointer");
+  LL_CHECK_ARG(M >= 1 && M <= 128, "ll_int4_gemm_tc serves 1 <= M <= 128 rows (got %d); larger M: ll_get_weight + ll_gemm_bf16_tc", M);
+  if (N <= 0 || K <= 0 || group <= 0 || N % W4_BN != 0 || group % W4_KB != 0 || K % group != 0) {
+    set_error("ll_int4_gemm_tc needs N %% 128 == 0 and group %% 128 == 0 (N=%d K=%d group=%d)", N, K, group);
+    return LL_ERR_UNSUPPORTED;
+  }
+  LL_CHECK_ARG(((uintptr_t)x & 15) == 0 && ((uintptr_t)w_stream & 15) == 0, "x / stream must be 16-byte aligned");
+  const int sms = sm_count();
+  W4Params p;
+  p.w = w_stream; p.y = (__nv_bfloat16*)y; p.scratch = scratch; p.bias = (const __nv_bfloat16*)bias;
+  p.M = M; p.N = N; p.K = K; p.G = K / W4_KB;
+  p.mpad = M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : 128;
+  p.ksplit = w4_pick_ksplit(N / W4_BN, p.G, sms > 0 ? sms : 148);
+  LL_CHECK_ARG(p.ksplit == 1 || scratch != nullptr, "this shape splits K %d ways: pass ll_int4_gemm_tc_scratch_bytes() of scratch", p.ksplit);
+  CUtensorMap mx;
+  if (int r = make_map(x, M, K, p.mpad, &mx)) return r;
+  cudaStream_t st = (cudaStream_t)stream;
+  int r;
+  if (p.mpad == 16) r = launch_w4<16>(mx, p, st);
+  else if (p.mpad == 32) r = launch_w4<32>(mx, p, st);
+  else if (p.mpad == 64) r = launch_w4<64>(mx, p, st);
+  else r = launch_w4<128>(mx, p, st);
+  if (r) return r;
+  if (p.ksplit > 1) {
+    const size_t n = (size_t)M * N;
+    w4_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(scratch, p.bias, p.y, M, N, p.ksplit, p.mpad);
+    LL_LAUNCH_OK("w4_reduce_kernel");
+  }
+  return LL_OK;
 }
 
 }  // extern "C"

@@ -92,7 +92,14 @@ __device__ __forceinline__ unsigned long long gtimer() {
 #ifdef LLB_TRACE
 #define TRACE(i)                                                                   \
   do {                                                                             \
-    if (p.trace != nullptr && threadIdx.x == 0) p.trace[blockIdx.x * 16 + (i)] = gtimer(); \
+    if (p.trace != nullptr && threadIdx.x == 0) {                                  \
+      p.trace[blockIdx.x * 16 + (i)] = gtimer();                                   \
+      if ((i) == 0) {                                                              \
+        unsigned sm_;                                                              \
+        asm volatile("mov.u32 %0, %smid;" : "=r"(sm_));                            \
+        p.trace[blockIdx.x * 16 + 14] = sm_ + 1;                                   \
+      }                                                                            \
+    }                                                                              \
   } while (0)
 #else
 #define TRACE(i) do { } while (0)
@@ -1330,9 +1337,12 @@ int specialise_level() {
 
 // Plan of the batch-1 integer-MMA kernel (stream kind 1): same tile split and ring as the bf16 kernel; shared memory holds
 // four digit planes of x instead of bf16 rows.
-bool i8_shape_ok(int N, int K, int group, int M) {
-  return M == 1 && group > 0 && group % I8_KB == 0 && K % group == 0 && N % TILE_N == 0 && (K / I8_KB) % I8_BPW == 0;
+// kind-1 stream: any whole number of 128-element k-blocks per scale group; the batch-1 GEMV additionally wants an even
+// number of k-blocks (the two blocks a warp takes from a chunk share their tile)
+bool i8_stream_ok(int N, int K, int group) {
+  return group > 0 && group % I8_KB == 0 && K > 0 && K % group == 0 && N > 0 && N % TILE_N == 0;
 }
+bool i8_shape_ok(int N, int K, int group, int M) { return M == 1 && i8_stream_ok(N, K, group) && (K / I8_KB) % I8_BPW == 0; }
 
 int make_plan_i8(int N, int K, int group, int nmat, int grid, bool has_norm, Plan* pl) {
   if (!i8_shape_ok(N, K, group, 1)) {
@@ -1462,8 +1472,8 @@ int ll_int4_prepare(const uint8_t* qw, const void* scales, const void* zeros, in
   LL_CHECK_ARG(qw && scales && zeros && out && status, "null pointer");
   LL_CHECK_ARG(kind == LL_STREAM_BF16 || kind == LL_STREAM_U8, "bad stream kind %d", kind);
   if (kind == LL_STREAM_U8) {
-    if (!i8_shape_ok(N, K, group, 1)) {
-      set_error("int4_prepare: stream kind 1 needs group %% 128 == 0, K %% 256 == 0, N %% 16 == 0 (N=%d K=%d group=%d)", N, K, group);
+    if (!i8_stream_ok(N, K, group)) {
+      set_error("int4_prepare: stream kind 1 needs group %% 128 == 0, K %% group == 0, N %% 16 == 0 (N=%d K=%d group=%d)", N, K, group);
       return LL_ERR_UNSUPPORTED;
     }
     LL_CHECK_ARG(((uintptr_t)out & 15) == 0, "stream buffer must be 16-byte aligned");

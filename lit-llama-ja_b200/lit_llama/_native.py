@@ -68,6 +68,8 @@ EXPORTS = {
     "ll_int4_gemv_plan": ([i32, i32, i32, i32, i32, i32, C.POINTER(sz_t), C.POINTER(C.c_int32)], C.c_int),
     "ll_int4_gemv": ([C.POINTER(GemvArgs), vp], C.c_int),
     "ll_gemm_bf16_tc": ([vp, vp, vp, vp, i32, i32, i32, vp], C.c_int),
+    "ll_int4_gemm_tc_scratch_bytes": ([i32, i32, i32], sz_t),
+    "ll_int4_gemm_tc": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, vp], C.c_int),
     "ll_int8_quantize_weight": ([vp, i32, vp, vp, i32, i32, vp], C.c_int),
     "ll_int8_workspace_bytes": ([i32, i32, i32], sz_t),
     "ll_int8_linear": ([vp, i32, vp, vp, vp, vp, i32, i32, i32, C.c_float, vp, sz_t, vp], C.c_int),
@@ -109,6 +111,11 @@ def call(name: str, *args) -> None:
     global LAUNCHES
     check(_fn[name](*args), name)
     LAUNCHES += 1
+
+
+def call_ret(name: str, *args):
+    """A query that returns a value (no launch, no error code)."""
+    return _fn[name](*args)
 
 
 def require_cuda(*tensors: torch.Tensor) -> None:

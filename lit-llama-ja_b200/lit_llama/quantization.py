@@ -115,6 +115,9 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         if not self._fast_eligible():
             return None
         kind = N.stream_kind(self.out_features, self.in_features, self.tile_cols, M)
+        return self._prepare_kind(kind)
+
+    def _prepare_kind(self, kind: int):
         ent = self._streams.get(kind)
         if ent is not None and ent[0] == self._state_key():
             return ent[1] if ent[2] else None
@@ -129,6 +132,14 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         ok = int(status.item()) == 0
         self._streams[kind] = (self._state_key(), buf, ok)
         return buf if ok else None
+
+    FUSED_GEMM_MAX_M = 128
+
+    def _fused_gemm_eligible(self, x) -> bool:
+        """9 <= M <= 128 bf16 rows on a layer whose scale groups are multiples of 128: the fused tcgen05 de-quantise + GEMM."""
+        return (self.bits == 4 and x.dtype == torch.bfloat16 and self.scales.dtype == torch.bfloat16
+                and self.out_features % 128 == 0 and self.tile_cols % 128 == 0 and self.in_features % self.tile_cols == 0
+                and (self.bias is None or self.bias.dtype == torch.bfloat16))
 
     def stream_for(self, M: int):
         """(prepared stream, its kind) for batch ``M`` WITHOUT building it (safe under CUDA-graph capture), or (None, kind)."""
@@ -160,6 +171,8 @@ class ColBlockQuantizedLinear(torch.nn.Module):
             fast = self.prepare(M) is not None
         if fast:
             self._gemv(x, y)
+        elif M <= self.FUSED_GEMM_MAX_M and self._fused_gemm_eligible(x) and self._fused_gemm(x, y):
+            pass
         elif M <= 16:
             assert inp.dtype in (torch.float32, torch.bfloat16)
             N.call("ll_qlinear_simt", N.ptr(x), N.dtype_code(x.dtype), M, N.ptr(qw), N.ptr(self.scales.contiguous()),
@@ -168,6 +181,25 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         else:
             y = dequant_gemm(self, x)
         return y.reshape(out_shape)
+
+    def _fused_gemm(self, x, y) -> bool:
+        """``ll_int4_gemm_tc``: weights streamed once in packed form, de-quantised in the main loop (False if the stream
+        cannot be built here, e.g. under CUDA-graph capture before it was prepared)."""
+        ent = self._streams.get(N.STREAM_U8)
+        if ent is not None and ent[0] == self._state_key():
+            w = ent[1] if ent[2] else None
+        elif torch.cuda.is_current_stream_capturing():
+            return False
+        else:
+            w = self._prepare_kind(N.STREAM_U8)
+        if w is None:
+            return False
+        M = x.shape[0]
+        nbytes = N.call_ret("ll_int4_gemm_tc_scratch_bytes", M, self.out_features, self.in_features)
+        scratch = _int8_workspace(x.device, nbytes) if nbytes else None
+        N.call("ll_int4_gemm_tc", N.ptr(w), N.ptr(x), N.ptr(self.bias), N.ptr(y), N.ptr(scratch), M, self.out_features,
+               self.in_features, self.tile_cols, N.stream())
+        return True
 
     def _gemv(self, x, y, *, pdl=False, grid=0):
         a = N.GemvArgs()

@@ -414,3 +414,31 @@ def test_specialised_gemv_epilogues_with_fused_norm_at_7b_shapes(M):
     m1 = 1 if M == 1 else 0
     for e, n in ((NV.EPI_ROPE_KV, 1), (NV.EPI_RESIDUAL, 0), (NV.EPI_SWIGLU, 1), (NV.EPI_STORE, 1)):
         assert spec[e, n, m1] > 0, spec.tolist()
+
+
+@pytest.mark.parametrize("M", [1, 2])
+@pytest.mark.parametrize("N_,K", [(4096, 4096), (1040, 11008)])
+def test_gemv_writes_nothing_outside_its_output(M, N_, K):
+    """compute-sanitizer is closed on this pool (profiles/r02_sanitizer_closed.txt): stray stores are looked for directly -
+    the output rows sit between canary rows that must come back untouched (both kernels, a ragged last CTA share)."""
+    from lit_llama import _native as NV
+    from oracle import quant as OQ
+
+    group = 128
+    pk, s, z = _bf16_layer(N_, K, group, 31)
+    lin = _stream_of(pk, s, z, N_, K, group, M)
+    x = OQ.bf16_round(np.random.RandomState(3).randn(M, K).astype(np.float32))
+    buf = torch.full((M + 2, N_), 1234.0, device=DEV, dtype=torch.bfloat16)
+    a = NV.GemvArgs()
+    w, a.stream_kind = lin.stream_for(M)
+    a.w = w.data_ptr()
+    a.N, a.K, a.group, a.M = N_, K, group, M
+    xd = torch.from_numpy(x).to(DEV, torch.bfloat16)
+    a.x, a.y = xd.data_ptr(), buf[1:].data_ptr()
+    a.epilogue, a.flags, a.grid = NV.EPI_STORE, 0, 0
+    NV.gemv(a)
+    torch.cuda.synchronize()
+    got = buf.float().cpu().numpy()
+    assert (got[0] == 1234.0).all() and (got[-1] == 1234.0).all(), "the GEMV wrote outside its output rows"
+    exact = _exact(x, pk, s, z, group)
+    assert (np.abs(got[1:-1] - exact) <= np.abs(exact) * 2.0 ** -8 + _mag(x, pk, s, z, group) * 2.0 ** -18 + 1e-30).all()

@@ -315,3 +315,58 @@ def test_int4_large_m_linear_vs_oracle(N, K, tile, M):
     mag = np.abs(x).astype(np.float64) @ np.abs(OQ.get_weight(packed, s, z, 4, tile, "bf16")).astype(np.float64).T
     assert (np.abs(y - ref) <= np.abs(ref) * 2.0**-7 + mag * 2.0**-16).all()
     assert (y != ref).mean() <= 0.05
+
+
+@pytest.mark.parametrize("N,K,tile,M", [
+    (4096, 4096, 128, 9), (4096, 4096, 128, 16), (4096, 4096, 128, 17), (4096, 4096, 128, 33), (11008, 4096, 128, 64),
+    (4096, 11008, 128, 65), (4096, 11008, 128, 128), (12288, 4096, -1, 12), (32000, 4096, 128, 24), (128, 128, 128, 10),
+    (256, 384, 128, 128),
+])
+def test_int4_fused_dequant_gemm_vs_oracle(N, K, tile, M):
+    """9 <= M <= 128 rows: ll_int4_gemm_tc streams the packed weights once and de-quantises them in the main loop
+    (tcgen05, weights in tensor memory) with the reference's bf16 rounding steps: == F.linear(x, get_weight(bf16)) of the
+    reference's fallback branch up to the fp32 summation order.  Shapes: the 7B layers, per-row scales, one k-block, an odd
+    number of k-blocks, every M padding class and its edges."""
+    import ctypes as C
+    from lit_llama import _native as NV
+
+    packed, s, z = _bf16_layer(N, K, tile, N + K + M)
+    lin = make_lin(N, K, 4, tile, s, z, "bf16", packed)
+    x = OQ.bf16_round(np.random.RandomState(1).randn(M, K).astype(np.float32))
+    xd = torch.from_numpy(x).to(DEV, torch.bfloat16)
+    assert lin._fused_gemm_eligible(xd)
+    NV.lib.ll_debug_gemv_counts  # (library loaded)
+    y = lin(xd).float().cpu().numpy()
+    assert NV.STREAM_U8 in lin._streams, "the fused path did not run (no kind-1 stream was built)"
+    ref = OQ.linear_forward(x, packed, s, z, None, 4, tile, "bf16")
+    mag = np.abs(x).astype(np.float64) @ np.abs(OQ.get_weight(packed, s, z, 4, tile, "bf16")).astype(np.float64).T
+    assert (np.abs(y - ref) <= np.abs(ref) * 2.0**-7 + mag * 2.0**-16).all(), float(np.abs(y - ref).max())
+    assert (y != ref).mean() <= 0.05
+    y2 = lin(xd).float().cpu().numpy()
+    assert np.array_equal(y, y2)            # fixed-order split-K sum: same bits run to run
+
+
+def test_int4_fused_dequant_gemm_bias_and_fractional_zero():
+    """bias is added after the split-K sum; a zero that is not an integer goes through bf16(q - zero) like get_weight."""
+    N_, K, tile, M = 512, 1024, 128, 20
+    packed, s, z = _bf16_layer(N_, K, tile, 77)
+    z = OQ.bf16_round(z + 0.3)
+    r = np.random.RandomState(5)
+    bias = OQ.bf16_round(r.randn(N_).astype(np.float32))
+    from lit_llama.quantization import ColBlockQuantizedLinear
+
+    torch.set_default_dtype(torch.bfloat16)
+    try:
+        lin = ColBlockQuantizedLinear(K, N_, True, bits=4, tile_cols=tile)
+    finally:
+        torch.set_default_dtype(torch.float32)
+    lin = lin.to(DEV)
+    lin.scales.copy_(torch.from_numpy(s)); lin.zeros.copy_(torch.from_numpy(z)); lin.bias.copy_(torch.from_numpy(bias))
+    lin.quant_weight.copy_(torch.from_numpy(packed))
+    x = OQ.bf16_round(r.randn(M, K).astype(np.float32))
+    y = lin(torch.from_numpy(x).to(DEV, torch.bfloat16)).float().cpu().numpy()
+    from lit_llama import _native as NV
+    assert NV.STREAM_U8 in lin._streams
+    ref = OQ.linear_forward(x, packed, s, z, bias, 4, tile, "bf16")
+    mag = np.abs(x).astype(np.float64) @ np.abs(OQ.get_weight(packed, s, z, 4, tile, "bf16")).astype(np.float64).T
+    assert (np.abs(y - ref) <= np.abs(ref) * 2.0**-7 + mag * 2.0**-16 + 2.0**-8 * np.abs(bias)).all()
