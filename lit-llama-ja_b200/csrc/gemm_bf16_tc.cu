@@ -284,6 +284,7 @@ int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* C, 
 //    the batch-1 GEMV's stream: no second copy of the weights), forms bf16((q - zero) * scale) with the reference's two
 //    bf16 roundings (HSUB2.BF16 exact for integer zeros, HMUL2.BF16 rounded) and writes 16 k per tcgen05.st;
 //    the ACTIVATIONS are the B operand, TMA-loaded [M_pad][64 k] tiles (128-byte swizzle); D[128][M_pad] fp32 in TMEM.
+//    Eight de-quantising warps: two per TMEM lane quarter, each takes half of a block's k (the arithmetic is ALU-bound).
 //  * one thread issues tcgen05.mma (128 x M_pad x 16, A from TMEM); A is double-buffered (2 x 64 columns) so that
 //    de-quantising k-block i + 1 overlaps the MMAs of block i; a 4-stage TMA ring feeds packed blocks and x tiles.
 //  * work unit = (128-column tile, k-range): K is split so that the units fill the SMs; partial sums go to a scratch
@@ -291,7 +292,7 @@ int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* C, 
 constexpr int W4_BN = 128;          // output columns per unit = TMEM lanes
 constexpr int W4_KB = 128;          // k per block of the packed stream
 constexpr int W4_BLK = W4_KB * 8 + 64;
-constexpr int W4_STAGES = 4;
+__host__ __device__ constexpr int w4_stages(int) { return 4; }
 
 __device__ __forceinline__ void umma_ts_bf16(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
   asm volatile(
@@ -331,12 +332,17 @@ struct W4Params {
   const uint8_t* w;       // stream kind 1: [N/16][K/128] blocks of 1088 B
   __nv_bfloat16* y;       // [M][N] (written directly when ksplit == 1)
   float* scratch;         // [tiles][ksplit][M_pad][128] partial sums (ksplit > 1)
+  int32_t* counters;      // [tiles] arrivals of a tile's k-splits (left zero)
   const __nv_bfloat16* bias;
   int M, N, K, G, ksplit, mpad;
 };
 
+constexpr bool W4_REDUCE_IN_KERNEL = false;
+constexpr int W4_DW = 8;  // de-quantising warps: two per TMEM lane quarter, each takes half of a block's k
 template <int MPAD>
-__global__ void __launch_bounds__(192, 1) gemm_w4_tc_kernel(const __grid_constant__ CUtensorMap map_x, const W4Params p) {
+__global__ void __launch_bounds__(64 + 32 * W4_DW, 1) gemm_w4_tc_kernel(const __grid_constant__ CUtensorMap map_x, const W4Params p) {
+  constexpr int W4_STAGES = w4_stages(MPAD);
+  __shared__ int s_last;
   constexpr int W_BYTES = 8 * W4_BLK;        // eight 16-column blocks of the stream = 128 columns x 128 k
   constexpr int X_ATOM = MPAD * 128;         // [MPAD][64 k] bf16, swizzled
   constexpr int X_BYTES = 2 * X_ATOM;
@@ -360,10 +366,10 @@ __global__ void __launch_bounds__(192, 1) gemm_w4_tc_kernel(const __grid_constan
     prefetch_tensormap(&map_x);
     for (int i = 0; i < W4_STAGES; ++i) {
       mbar_init(&full[i], 1);
-      mbar_init(&empty[i], 5);  // 4 de-quantising warps + the MMA commit
+      mbar_init(&empty[i], W4_DW + 1);  // the de-quantising warps + the MMA commit
     }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&a_ready[i], 4);
+      mbar_init(&a_ready[i], W4_DW);
       mbar_init(&a_free[i], 1);
     }
     mbar_init(tmem_full, 1);
@@ -429,8 +435,9 @@ __global__ void __launch_bounds__(192, 1) gemm_w4_tc_kernel(const __grid_constan
       umma_commit(tmem_full);
     }
   } else {
-    // ===================== de-quantising warps 2..5, then the epilogue =====================
+    // ===================== de-quantising warps 2.., then the epilogue =====================
     const int quarter = warp & 3;            // a warp may only touch TMEM lanes [32 * (warpid % 4), +32)
+    const int khalf = (warp - 2) >> 2;       // which half of a block's k this warp de-quantises (W4_DW = 8)
     const int t = quarter * 32 + lane;       // TMEM lane = output column n0 + t
     const int t16 = t >> 4, g = t & 7, hi = (t >> 3) & 1;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
@@ -447,9 +454,15 @@ __global__ void __launch_bounds__(192, 1) gemm_w4_tc_kernel(const __grid_constan
       asm volatile("ld.shared.u32 %0, [%1];" : "=r"(sz) : "r"(blk + 1024u + (uint32_t)(2 * g + hi) * 4u));
       const uint32_t s2 = (sz & 0xffffu) * 0x00010001u;  // bf16x2 (scale, scale)
       const uint32_t z2 = ((sz >> 16) ^ 0x8000u) * 0x00010001u;  // tail holds -zero: bf16x2 (zero, zero)
+      // an integer zero (every RTN / GPTQ checkpoint): (128 + q) - (128 + zero) in ONE exact subtraction
+      const float zf = __uint_as_float((sz & 0xffff0000u) ^ 0x80000000u);
+      const bool zint = zf == floorf(zf) && zf >= 0.f && zf <= 64.f;
+      const uint32_t zc2 = zint ? (uint32_t)(0x4300u + (uint32_t)zf) * 0x00010001u : 0x43004300u;
       const uint32_t ta = lane_addr + 128u + (uint32_t)buf * 64u;
+      constexpr int MPW = 8 * 4 / W4_DW;  // 16-k slices per warp per block
 #pragma unroll
-      for (int m = 0; m < 8; ++m) {  // m = 2 tig + q: k = 32 tig + 16 q + 0..15 of the block -> TMEM columns 16 tig + 8 q + 0..7
+      for (int mm = 0; mm < MPW; ++mm) {  // m = 2 tig + q: k = 32 tig + 16 q + 0..15 of the block -> TMEM columns 16 tig + 8 q + 0..7
+        const int m = (W4_DW == 8 ? khalf * 4 : 0) + mm;
         const int tig = m >> 1, q = m & 1;
         uint4 wq;
         asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wq.x), "=r"(wq.y), "=r"(wq.z), "=r"(wq.w)
@@ -461,10 +474,14 @@ __global__ void __launch_bounds__(192, 1) gemm_w4_tc_kernel(const __grid_constan
           const uint32_t nib = (w[j] >> sh) & 0x0F0F0F0Fu;          // this column's four nibbles (k, k+1, k+2, k+3)
           // bf16 (128 + q) = 0x4300 | q; minus 128, minus zero (both exact for integer zeros), times scale (rounded):
           // the reference's get_weight in bf16 (quantization.py:399-408)
-          const uint32_t a = w4_sub2(w4_prmt(nib, 0x43434343u, 0x5140u), 0x43004300u);
-          const uint32_t b = w4_sub2(w4_prmt(nib, 0x43434343u, 0x5342u), 0x43004300u);
-          r[2 * j] = w4_mul2(w4_sub2(a, z2), s2);
-          r[2 * j + 1] = w4_mul2(w4_sub2(b, z2), s2);
+          uint32_t a = w4_sub2(w4_prmt(nib, 0x43434343u, 0x5140u), zc2);
+          uint32_t b = w4_sub2(w4_prmt(nib, 0x43434343u, 0x5342u), zc2);
+          if (!zint) {
+            a = w4_sub2(a, z2);
+            b = w4_sub2(b, z2);
+          }
+          r[2 * j] = w4_mul2(a, s2);
+          r[2 * j + 1] = w4_mul2(b, s2);
         }
         tmem_st_x8(ta + (uint32_t)(16 * tig + 8 * q), r);
       }
@@ -480,13 +497,15 @@ __global__ void __launch_bounds__(192, 1) gemm_w4_tc_kernel(const __grid_constan
         phase ^= 1u;
       }
     }
-    // ---- epilogue: D[t][m] for m < M: thread t holds output column n0 + t
+    // ---- epilogue: D[t][m] for m < M: thread t holds output column n0 + t; the two warps of a lane quarter share the
+    //      M_pad accumulator columns
     mbar_wait_parity(tmem_full, 0);
     tc_fence_after();
     const int n = tile * W4_BN + t;
+    constexpr int EW = W4_DW / 4;  // warps per lane quarter
     const float bias = (p.bias != nullptr && p.ksplit == 1) ? __bfloat162float(p.bias[n]) : 0.f;
 #pragma unroll 1
-    for (int c0 = 0; c0 < MPAD; c0 += 16) {
+    for (int c0 = 16 * khalf; c0 < MPAD; c0 += 16 * EW) {
       uint32_t v[16];
       asm volatile(
           "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
@@ -511,9 +530,33 @@ __global__ void __launch_bounds__(192, 1) gemm_w4_tc_kernel(const __grid_constan
     tc_fence_after();
     tmem_dealloc(tmem_base, 256);
   }
+  // (Measured, profiles/r02_fused_gemm.md: reducing inside the kernel - the last k-split to arrive sums the tile - and two
+  // CTAs per SM were both SLOWER than a separate reduce kernel and one CTA per SM: 2.95 -> 3.76 ms per 161 Linears at
+  // batch 32.  The code stays behind a constant for the record.)
+  if (W4_REDUCE_IN_KERNEL && p.ksplit > 1) {
+    // the k-split that arrives last adds the tile's partial sums in SPLIT order (the same bits whoever is last), adds the
+    // bias, rounds and stores; the counter goes back to zero for the next launch
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = (atomicAdd(&p.counters[tile], 1) == p.ksplit - 1);
+    __syncthreads();
+    if (s_last) {
+      __threadfence();
+      const float* base_t = p.scratch + (size_t)tile * p.ksplit * MPAD * W4_BN;
+      for (int e = threadIdx.x; e < p.M * W4_BN; e += blockDim.x) {
+        const int m = e / W4_BN, tt = e - m * W4_BN;
+        float acc = 0.f;
+        for (int k2 = 0; k2 < p.ksplit; ++k2) acc += __ldcg(base_t + ((size_t)k2 * MPAD + m) * W4_BN + tt);
+        const int n = tile * W4_BN + tt;
+        if (p.bias != nullptr) acc += __bfloat162float(p.bias[n]);
+        p.y[(size_t)m * p.N + n] = __float2bfloat16_rn(acc);
+      }
+      if (threadIdx.x == 0) p.counters[tile] = 0;
+    }
+  }
 }
 
-// y[m][n] = bf16(sum over the k-splits, in split order, + bias)
+// y[m][n] = bf16(sum over the k-splits, in split order, + bias)   
 __global__ void w4_reduce_kernel(const float* __restrict__ scratch, const __nv_bfloat16* __restrict__ bias,
                                  __nv_bfloat16* __restrict__ y, int M, int N, int ksplit, int mpad) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -528,6 +571,7 @@ __global__ void w4_reduce_kernel(const float* __restrict__ scratch, const __nv_b
 
 template <int MPAD>
 int launch_w4(const CUtensorMap& mx, const W4Params& p, cudaStream_t st) {
+  constexpr int W4_STAGES = w4_stages(MPAD);
   constexpr size_t stage = ((8 * W4_BLK + 1023) / 1024) * 1024 + 2 * MPAD * 128;
   constexpr size_t smem = W4_STAGES * stage + (2 * W4_STAGES + 5) * 8 + 16 + 1024;
   static bool configured = false;
@@ -535,7 +579,7 @@ int launch_w4(const CUtensorMap& mx, const W4Params& p, cudaStream_t st) {
     LL_CUDA(cudaFuncSetAttribute(gemm_w4_tc_kernel<MPAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
-  gemm_w4_tc_kernel<MPAD><<<(p.N / W4_BN) * p.ksplit, 192, smem, st>>>(mx, p);
+  gemm_w4_tc_kernel<MPAD><<<(p.N / W4_BN) * p.ksplit, 64 + 32 * W4_DW, smem, st>>>(mx, p);
   LL_LAUNCH_OK("gemm_w4_tc_kernel");
   return LL_OK;
 }
@@ -586,6 +630,28 @@ size_t ll_int4_gemm_tc_scratch_bytes(int M, int N, int K) {
   return ks == 1 ? 0 : (size_t)(N / W4_BN) * ks * mpad * W4_BN * sizeof(float);
 }
 
+namespace {
+// per-device arrival counters of the k-splits (one int per 128-column tile; the kernels leave them zero), allocated on
+// first use outside stream capture
+int32_t* w4_counters(int tiles, cudaStream_t st) {
+  static int32_t* buf[16] = {};
+  static int cap[16] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
+  if (cap[dev] < tiles) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return nullptr;
+    const int n = tiles < 4096 ? 4096 : tiles;
+    int32_t* nb = nullptr;
+    if (cudaMalloc(&nb, (size_t)n * sizeof(int32_t)) != cudaSuccess) return nullptr;
+    cudaMemset(nb, 0, (size_t)n * sizeof(int32_t));
+    buf[dev] = nb;   // (an older, smaller buffer stays alive: captured graphs may hold it)
+    cap[dev] = n;
+  }
+  return buf[dev];
+}
+}  // namespace
+
 int ll_int4_gemm_tc(const uint8_t* w_stream, const void* x, const void* bias, void* y, float* scratch, int M, int N, int K,
                     int group, ll_stream stream) {
   LL_CHECK_ARG(w_stream && x && y, "null pointer");
@@ -605,13 +671,21 @@ int ll_int4_gemm_tc(const uint8_t* w_stream, const void* x, const void* bias, vo
   CUtensorMap mx;
   if (int r = make_map(x, M, K, p.mpad, &mx)) return r;
   cudaStream_t st = (cudaStream_t)stream;
+  p.counters = nullptr;
+  if (W4_REDUCE_IN_KERNEL && p.ksplit > 1) {
+    p.counters = w4_counters(N / W4_BN, st);
+    if (p.counters == nullptr) {
+      set_error("ll_int4_gemm_tc: could not allocate the split counters (first call under stream capture?)");
+      return LL_ERR_CUDA;
+    }
+  }
   int r;
   if (p.mpad == 16) r = launch_w4<16>(mx, p, st);
   else if (p.mpad == 32) r = launch_w4<32>(mx, p, st);
   else if (p.mpad == 64) r = launch_w4<64>(mx, p, st);
   else r = launch_w4<128>(mx, p, st);
   if (r) return r;
-  if (p.ksplit > 1) {
+  if (!W4_REDUCE_IN_KERNEL && p.ksplit > 1) {
     const size_t n = (size_t)M * N;
     w4_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(scratch, p.bias, p.y, M, N, p.ksplit, p.mpad);
     LL_LAUNCH_OK("w4_reduce_kernel");

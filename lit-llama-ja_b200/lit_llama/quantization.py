@@ -133,7 +133,10 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         self._streams[kind] = (self._state_key(), buf, ok)
         return buf if ok else None
 
-    FUSED_GEMM_MAX_M = 128
+    FUSED_GEMM_MAX_M = 128       # rows one ll_int4_gemm_tc call takes
+    # rows up to which the fused kernel is looped over 128-row blocks (each block streams the packed weights again) instead of
+    # unpacking W to bf16 once and running the plain tcgen05 GEMM (measured cross-over: profiles/r02_fused_gemm.md)
+    FUSED_GEMM_LOOP_MAX_M = int(__import__("os").environ.get("LLB200_FUSED_GEMM_MAX_M", 256))
 
     def _fused_gemm_eligible(self, x) -> bool:
         """9 <= M <= 128 bf16 rows on a layer whose scale groups are multiples of 128: the fused tcgen05 de-quantise + GEMM."""
@@ -171,7 +174,8 @@ class ColBlockQuantizedLinear(torch.nn.Module):
             fast = self.prepare(M) is not None
         if fast:
             self._gemv(x, y)
-        elif M <= self.FUSED_GEMM_MAX_M and self._fused_gemm_eligible(x) and self._fused_gemm(x, y):
+        elif M <= max(self.FUSED_GEMM_MAX_M, self.FUSED_GEMM_LOOP_MAX_M) and self.FUSED_GEMM_MAX_M > 0 \
+                and self._fused_gemm_eligible(x) and self._fused_gemm(x, y):
             pass
         elif M <= 16:
             assert inp.dtype in (torch.float32, torch.bfloat16)
@@ -194,11 +198,14 @@ class ColBlockQuantizedLinear(torch.nn.Module):
             w = self._prepare_kind(N.STREAM_U8)
         if w is None:
             return False
-        M = x.shape[0]
-        nbytes = N.call_ret("ll_int4_gemm_tc_scratch_bytes", M, self.out_features, self.in_features)
-        scratch = _int8_workspace(x.device, nbytes) if nbytes else None
-        N.call("ll_int4_gemm_tc", N.ptr(w), N.ptr(x), N.ptr(self.bias), N.ptr(y), N.ptr(scratch), M, self.out_features,
-               self.in_features, self.tile_cols, N.stream())
+        step = self.FUSED_GEMM_MAX_M
+        for r0 in range(0, x.shape[0], step):
+            xb, yb = x[r0:r0 + step], y[r0:r0 + step]
+            M = xb.shape[0]
+            nbytes = N.call_ret("ll_int4_gemm_tc_scratch_bytes", M, self.out_features, self.in_features)
+            scratch = _int8_workspace(x.device, nbytes) if nbytes else None
+            N.call("ll_int4_gemm_tc", N.ptr(w), N.ptr(xb), N.ptr(self.bias), N.ptr(yb), N.ptr(scratch), M, self.out_features,
+                   self.in_features, self.tile_cols, N.stream())
         return True
 
     def _gemv(self, x, y, *, pdl=False, grid=0):
