@@ -115,6 +115,12 @@ LL_API int ll_int4_stream_kind(int N, int K, int group, int M);
 #define LL_EPI_PUSH 4     /* y_r[M][N] = x . W^T on every rank r (peer stores) + arrival counters, see push_dst */
 
 #define LL_GEMV_PDL 1 /* launch with programmatic stream serialization (prologue overlap) */
+/* Footprint parity of a batch-1 launch inside a PDL chain (stream kind 1 only).  Consecutive GEMVs of a chain alternate
+ * EVEN / ODD: an EVEN launch asks for 116 KB of shared memory (two EVEN CTAs cannot share an SM), an ODD launch carries
+ * two idle warps (two ODD CTAs exceed the register file), an EVEN + ODD pair fits - so the block scheduler can never put
+ * two CTAs of the SAME GEMV on one SM, whatever else is resident (profiles/r02_gemv_experiments.md section 6). */
+#define LL_GEMV_EVEN 4
+#define LL_GEMV_ODD 2
 
 typedef struct ll_gemv_args {
   const uint8_t* w;    /* repacked stream from ll_int4_prepare */

@@ -781,7 +781,7 @@ constexpr int I8_CH = I8_W * I8_BPW, I8_CHB = I8_CH * I8_BLK, I8_NCONS = I8_W * 
 constexpr uint32_t NIB_LO = 0x0F0F0F0Fu;
 
 template <int EPI, int NORM>
-__global__ void __launch_bounds__((I8_W + 1) * 32, 2) gemv_w4a8_kernel(const __grid_constant__ Params p) {
+__global__ void __launch_bounds__((I8_W + 9) * 32, 1) gemv_w4a8_kernel(const __grid_constant__ Params p) {
   constexpr int W = I8_W, BPW = I8_BPW, KB = I8_KB, BLK = I8_BLK, CH = I8_CH, CHB = I8_CHB, NCONS = I8_NCONS;
   constexpr int MAX_SLOTS_C = 12;
   constexpr int MT = TILE_N;  // floats per (tile, matrix) result at batch 1
@@ -815,6 +815,12 @@ __global__ void __launch_bounds__((I8_W + 1) * 32, 2) gemv_w4a8_kernel(const __g
   }
   __syncthreads();
   pdl_launch_dependents();
+  if (warp > W) {
+    // idle warps of an ODD-parity launch: they only widen the CTA's register footprint, so they must stay resident (an
+    // exited warp gives its registers back) - parked on a named barrier that warp 0 releases at the end
+    asm volatile("bar.sync 2, %0;" ::"r"((int)blockDim.x - W * 32) : "memory");
+    return;
+  }
 
   if (warp == W) {
     // =============================== producer warp (as in the bf16 kernel) ===============================
@@ -1178,6 +1184,7 @@ __global__ void __launch_bounds__((I8_W + 1) * 32, 2) gemv_w4a8_kernel(const __g
     __syncwarp();
   }
   TRACE(6);
+  if (blockDim.x > (W + 1) * 32 && warp == 0) asm volatile("bar.arrive 2, %0;" ::"r"((int)blockDim.x - W * 32) : "memory");
 }
 
 // stream kind 1: one thread per 32-bit word (and per tail entry)
@@ -1344,7 +1351,7 @@ bool i8_stream_ok(int N, int K, int group) {
 }
 bool i8_shape_ok(int N, int K, int group, int M) { return M == 1 && i8_stream_ok(N, K, group) && (K / I8_KB) % I8_BPW == 0; }
 
-int make_plan_i8(int N, int K, int group, int nmat, int grid, bool has_norm, Plan* pl) {
+int make_plan_i8(int N, int K, int group, int nmat, int grid, bool has_norm, Plan* pl, int budget = SMEM_CORESIDENT) {
   if (!i8_shape_ok(N, K, group, 1)) {
     set_error("int4 GEMV (stream kind 1) needs M = 1, N %% 16 == 0, group %% 128 == 0, K %% 256 == 0 (N=%d K=%d group=%d)", N, K, group);
     return LL_ERR_UNSUPPORTED;
@@ -1383,7 +1390,7 @@ int make_plan_i8(int N, int K, int group, int nmat, int grid, bool has_norm, Pla
   q.off_nw = take(has_norm ? (size_t)K * 2 : 0);
   const size_t chb = (size_t)I8_CHB;
   const int nch_max = (ipc_max + I8_CH - 1) / I8_CH;
-  long s = ((long)SMEM_CORESIDENT - (long)fixed) / (long)chb;
+  long s = ((long)budget - (long)fixed) / (long)chb;
   if (s < 3 && nch_max > s) s = ((long)SMEM_SOLO - (long)fixed) / (long)chb;
   if (s > MAX_SLOTS) s = MAX_SLOTS;
   if (s > nch_max) s = nch_max;
@@ -1399,15 +1406,37 @@ int make_plan_i8(int N, int K, int group, int nmat, int grid, bool has_norm, Pla
   return LL_OK;
 }
 
+constexpr int SMEM_EVEN = 116 * 1024;  // two EVEN CTAs (2 x 116 + 2 KB) exceed an SM's 228 KB; EVEN + ODD (116 + 108 + 2) fit
+constexpr int SMEM_ODD = 108 * 1024;
+int g_parity = 0;  // of the launch being issued: 0 none, LL_GEMV_EVEN, LL_GEMV_ODD
+
 template <int EPI, int NORM>
 int launch_i8(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
   static size_t configured = 0;
-  if (pl.smem > configured) {
-    if (configured == 0) prefer_max_smem(gemv_w4a8_kernel<EPI, NORM>);
-    LL_CUDA(cudaFuncSetAttribute(gemv_w4a8_kernel<EPI, NORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
-    configured = pl.smem;
+  size_t smem = pl.smem;
+  int threads = (I8_W + 1) * 32;
+  if (g_parity == LL_GEMV_EVEN && smem < (size_t)SMEM_EVEN) smem = SMEM_EVEN;  // the footprint, not the ring, is the point
+  if (g_parity == LL_GEMV_ODD && smem <= (size_t)SMEM_ODD) {
+    // idle warps until two of these CTAs need more than the 64 K registers of an SM (and one still fits beside an EVEN CTA
+    // of 288 threads x <= 96 registers)
+    static int odd_threads = 0;
+    if (odd_threads == 0) {
+      cudaFuncAttributes fa;
+      LL_CUDA(cudaFuncGetAttributes(&fa, gemv_w4a8_kernel<EPI, NORM>));
+      const int regs = ((fa.numRegs + 7) / 8) * 8;
+      int t = ((32768 / regs) / 32 + 1) * 32;
+      if (t < threads + 64) t = threads + 64;
+      if (t > (I8_W + 9) * 32) t = (I8_W + 9) * 32;
+      odd_threads = t;
+    }
+    threads = odd_threads;
   }
-  LL_CUDA(launch(gemv_w4a8_kernel<EPI, NORM>, dim3(pl.P), dim3((I8_W + 1) * 32), pl.smem, st, pdl, p));
+  if (smem > configured) {
+    if (configured == 0) prefer_max_smem(gemv_w4a8_kernel<EPI, NORM>);
+    LL_CUDA(cudaFuncSetAttribute(gemv_w4a8_kernel<EPI, NORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  LL_CUDA(launch(gemv_w4a8_kernel<EPI, NORM>, dim3(pl.P), dim3(threads), smem, st, pdl, p));
   return LL_OK;
 }
 
@@ -1576,7 +1605,11 @@ int ll_int4_gemv(const ll_gemv_args* a, ll_stream stream) {
   LL_CHECK_ARG(a->stream_kind == LL_STREAM_BF16 || i8, "bad stream kind %d", a->stream_kind);
   if (i8) {
     LL_CHECK_ARG(a->M == 1 && a->epilogue != LL_EPI_PUSH, "stream kind 1 serves batch 1 with the store / residual / RoPE / SwiGLU epilogues");
-    if (int r = make_plan_i8(a->N, a->K, a->group, nmat, a->grid, a->norm_weight != nullptr, &pl)) return r;
+    const int par = (a->flags & LL_GEMV_PDL) ? (a->flags & (LL_GEMV_EVEN | LL_GEMV_ODD)) : 0;
+    g_parity = par == LL_GEMV_EVEN || par == LL_GEMV_ODD ? par : 0;
+    const int budget = g_parity == LL_GEMV_EVEN ? SMEM_EVEN : g_parity == LL_GEMV_ODD ? SMEM_ODD : SMEM_CORESIDENT;
+    if (int r = make_plan_i8(a->N, a->K, a->group, nmat, a->grid, a->norm_weight != nullptr, &pl, budget)) return r;
+    if (pl.smem > (size_t)budget) g_parity = 0;  // a row too long for the co-resident budget runs alone anyway
   } else if (int r = make_plan(a->N, a->K, a->group, nmat, a->M, a->grid, a->norm_weight != nullptr, &pl)) return r;
 
   Params p;

@@ -25,6 +25,7 @@ lib = C.CDLL(str(_LIB_PATH))
 LL_F32, LL_BF16, LL_F16 = 0, 1, 2
 EPI_STORE, EPI_RESIDUAL, EPI_ROPE_KV, EPI_SWIGLU, EPI_PUSH = 0, 1, 2, 3, 4
 GEMV_PDL = 1
+GEMV_ODD, GEMV_EVEN = 2, 4
 
 _DT = {torch.float32: LL_F32, torch.bfloat16: LL_BF16, torch.float16: LL_F16}
 

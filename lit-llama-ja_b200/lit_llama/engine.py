@@ -91,7 +91,10 @@ class DecodeEngine:
         self.use_graph = _env_flag("LLB200_GRAPH", True)
         # measured (profiles/r01_step_probe.md): launching the attention kernel itself with the programmatic
         # attribute costs ~8 us per block (its 512 waiting CTAs crowd the SMs the GEMV pair shares)
-        self.attn_pdl = _env_flag("LLB200_PDL_ATTN", False)
+        # LLB200_GEMV_PARITY=1: consecutive GEMVs alternate EVEN / ODD footprints (include/llb200.h) so that two CTAs of the
+        # same GEMV can never share an SM; the attention kernel can then be a programmatic dependent too
+        self.parity = _env_flag("LLB200_GEMV_PARITY", False) and self.use_pdl
+        self.attn_pdl = _env_flag("LLB200_PDL_ATTN", self.parity)
         self.n_launches = 0
         self.n_replays = 0
 
@@ -126,6 +129,8 @@ class DecodeEngine:
         pass
 
     # ------------------------------------------------------------------ argument blocks
+    _PARITY = {"attn": N.GEMV_EVEN, "proj": N.GEMV_ODD, "fc": N.GEMV_EVEN, "down": N.GEMV_ODD, "head": N.GEMV_EVEN}
+
     def _gemv_args(self, lin, x, y, epi, plan, norm=None, lin2=None):
         a = N.GemvArgs()
         w, a.stream_kind = lin.stream_for(self.B)
@@ -139,6 +144,8 @@ class DecodeEngine:
         if norm is not None:
             a.norm_weight, a.eps = norm.scale.data_ptr(), norm.eps
         a.epilogue, a.flags, a.grid = epi, (N.GEMV_PDL if self.use_pdl else 0), 0
+        if self.parity:
+            a.flags |= self._PARITY[plan]
         return a
 
     def _build_args(self):

@@ -207,6 +207,7 @@ class LLaMA(nn.Module):
     """ref: model.py:59-151 - same submodule names (state-dict keys), same ``forward`` signature."""
 
     use_fused_decode = True   # single-token int4/bf16 steps go through engine.DecodeEngine
+    use_step_graph = True     # other single-token steps with a KV cache (batch > 8, ...) replay one CUDA graph per (B, S)
 
     def __init__(self, config: LLaMAConfig) -> None:
         super().__init__()
@@ -225,6 +226,8 @@ class LLaMA(nn.Module):
         self.kv_caches: List[KVCache] = []
         self._rope_f32: Optional[torch.Tensor] = None
         self._engine = None
+        self._kv_pool = {}          # (shape, dtype, device) -> KV tensors: stable addresses across reset_cache()
+        self._step_graphs = {}      # (B, max_seq_length) -> captured single-token step of the per-module path
 
     def _init_weights(self, module: nn.Module) -> None:
         """ref: model.py:78-82"""
@@ -276,7 +279,50 @@ class LLaMA(nn.Module):
             eng = self._fused_engine(B, max_seq_length)
             if eng is not None:
                 return eng.forward_token(idx, input_pos)
+        if (use_cache and T == 1 and self.use_step_graph and self.use_fused_decode and B > 1 and input_pos.device.type == "cuda"
+                and not torch.cuda.is_current_stream_capturing() and __import__("os").environ.get("LLB200_STEP_GRAPH", "1") != "0"):
+            out = self._graphed_step(idx, max_seq_length, input_pos)
+            if out is not None:
+                return out
+        return self._forward_modules(idx, max_seq_length, input_pos)
 
+    def _graphed_step(self, idx, max_seq_length, input_pos):
+        """One decode step of the per-module path (batches the fused engine does not take) as ONE CUDA-graph replay: the
+        step is ~9 kernels per block and, launched eagerly, costs more host time than device time.  The position is read
+        from a device buffer by every kernel (ll_set_pos), so one capture per (batch, cache length) serves every token."""
+        B = idx.size(0)
+        key = (B, max_seq_length)
+        ent = self._step_graphs.get(key)
+        if ent is not None and (not self.kv_caches or self.kv_caches[0][0].data_ptr() != ent["kv0"]):
+            if not self.kv_caches and ent["kv"][0][0].shape[0] == B:
+                self.kv_caches = list(ent["kv"])          # after reset_cache(): the captured cache tensors are re-attached
+            else:
+                ent = None
+        if ent is None:
+            if not self.kv_caches or self.kv_caches[0][0].shape[2] != max_seq_length or self.kv_caches[0][0].shape[0] != B:
+                return None                                # no cache of this shape yet (the eager path allocates it)
+            s_idx, s_pos = idx.clone(), input_pos.clone()
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):                  # warm-up: workspaces, weight streams, kernel attributes
+                for _ in range(2):
+                    self._forward_modules(s_idx, max_seq_length, s_pos)
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                out = self._forward_modules(s_idx, max_seq_length, s_pos)
+            ent = self._step_graphs[key] = dict(graph=g, idx=s_idx, pos=s_pos, out=out, kv=list(self.kv_caches),
+                                                kv0=self.kv_caches[0][0].data_ptr())
+        ent["idx"].copy_(idx)
+        ent["pos"].copy_(input_pos)
+        ent["graph"].replay()
+        return ent["out"].clone()
+
+    def _forward_modules(self, idx: torch.Tensor, max_seq_length: int, input_pos: Optional[torch.Tensor]) -> torch.Tensor:
+        B, T = idx.size()
+        block_size = self.config.block_size
+        use_cache = input_pos is not None
         dev = idx.device
         pos3 = mask = None
         if use_cache:
@@ -301,12 +347,27 @@ class LLaMA(nn.Module):
         else:
             if not self.kv_caches:
                 shape = (B, self.transformer.h[0].attn.n_head, max_seq_length, self.config.head_size)
-                self.kv_caches = [(torch.zeros(shape, device=dev, dtype=x.dtype), torch.zeros(shape, device=dev, dtype=x.dtype))
-                                  for _ in range(self.config.n_layer)]
+                self.kv_caches = self._kv_from_pool(shape, x.dtype, dev)
             for i, block in enumerate(self.transformer.h):
                 x, self.kv_caches[i] = block(x, step, self.kv_caches[i])
         x = self.transformer.ln_f(x)
         return self.lm_head(x)
+
+    def _kv_from_pool(self, shape, dtype, dev):
+        """Zeroed KV tensors of this shape - the SAME tensors after every reset_cache(), so that captured step graphs
+        (which hold their addresses) stay valid; one set per shape (ref model.py:112-118 allocates fresh zeros each time)."""
+        key = (tuple(shape), dtype, str(dev))
+        kv = self._kv_pool.get(key)
+        if kv is None:
+            if len(self._kv_pool) >= 2:            # keep at most two shapes alive
+                self._kv_pool.pop(next(iter(self._kv_pool)))
+                self._step_graphs.clear()
+            kv = self._kv_pool[key] = [(torch.zeros(shape, device=dev, dtype=dtype), torch.zeros(shape, device=dev, dtype=dtype))
+                                       for _ in range(self.config.n_layer)]
+        else:
+            for k, v in kv:
+                k.zero_(); v.zero_()
+        return list(kv)
 
     def _fused_engine(self, B: int, max_seq_length: int):
         """The fused decode engine for this (batch, cache length), or None if the model is not

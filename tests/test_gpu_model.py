@@ -180,3 +180,28 @@ def test_ops_vs_reference_golden(golden):
     x = torch.from_numpy(g["rope.x"]).to(DEV)
     np.testing.assert_allclose(apply_rope(x, rope).cpu().numpy(), g["rope.fp32"], rtol=1e-6, atol=1e-6)
     assert np.array_equal(apply_rope(x.bfloat16(), rope).float().cpu().numpy(), g["rope.bf16"])
+
+
+def test_batched_decode_step_graph_matches_eager_launches():
+    """Batches the fused engine does not take run their single-token steps as one CUDA-graph replay per (B, S): same bits
+    as the eager per-module launches, for every position, and still valid after reset_cache() (the KV tensors are reused)."""
+    m = build_fp_model()
+    B, T, msl = 3, 12, 16
+    idx = torch.randint(0, TINY["vocab_size"], (B, T), generator=torch.Generator().manual_seed(3)).to(DEV)
+
+    def run(graph):
+        m.use_step_graph = graph
+        m.reset_cache()
+        out = []
+        with torch.no_grad():
+            out.append(m(idx[:, :6], msl, torch.arange(6, device=DEV))[:, -1])
+            for t in range(6, T):
+                out.append(m(idx[:, t:t + 1], msl, torch.tensor([t], device=DEV))[:, -1])
+        return torch.stack(out).cpu().numpy()
+
+    eager = run(False)
+    graphed = run(True)
+    assert (B, msl) in m._step_graphs, "the step graph was not used"
+    assert np.array_equal(eager, graphed)
+    assert np.array_equal(run(True), eager)       # second pass: same graph, re-used KV tensors
+    assert len(m._step_graphs) == 1
