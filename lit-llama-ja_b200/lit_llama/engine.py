@@ -93,7 +93,15 @@ class DecodeEngine:
         # attribute costs ~8 us per block (its 512 waiting CTAs crowd the SMs the GEMV pair shares)
         # LLB200_GEMV_PARITY=1: consecutive GEMVs alternate EVEN / ODD footprints (include/llb200.h) so that two CTAs of the
         # same GEMV can never share an SM; the attention kernel can then be a programmatic dependent too
-        self.parity = _env_flag("LLB200_GEMV_PARITY", False) and self.use_pdl
+        # (measured, profiles/r02_gemv_experiments.md section 6: every SM then holds exactly one CTA of each GEMV and the
+        # 7B step drops 1360 -> 1339 us).  Default: on where every Linear of the chain takes the integer-MMA kernel (the
+        # only one with the two footprints) on one GPU; off under tensor parallelism, where the plainly launched
+        # all-reduce kernels already separate the GEMVs.
+        lins = [model.lm_head]
+        for blk in model.transformer.h:
+            lins += [blk.attn.c_attn, _unwrap(blk.attn.c_proj)[0], blk.mlp.c_fc1, blk.mlp.c_fc2, _unwrap(blk.mlp.c_proj)[0]]
+        all_u8 = all(lin.stream_for(B)[1] == N.STREAM_U8 for lin in lins)
+        self.parity = _env_flag("LLB200_GEMV_PARITY", not self.tp) and self.use_pdl and all_u8
         self.attn_pdl = _env_flag("LLB200_PDL_ATTN", self.parity)
         self.n_launches = 0
         self.n_replays = 0

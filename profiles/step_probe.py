@@ -40,11 +40,13 @@ def timed_graph(fn, reps=20):
     return 1e3 * e0.elapsed_time(e1) / reps
 
 
-for pdl, apdl in ((True, os.environ.get("PROBE_APDL", "0") == "1"),):
+for pdl in (True,):
     os.environ["LLB200_PDL"] = "1" if pdl else "0"
-    os.environ["LLB200_PDL_ATTN"] = "1" if apdl else "0"
+    if "PROBE_APDL" in os.environ:          # otherwise the engine's own default (on with the EVEN/ODD footprints)
+        os.environ["LLB200_PDL_ATTN"] = os.environ["PROBE_APDL"]
     model.kv_caches.clear(); model._engine = None
     eng = model._fused_engine(1, S)
+    apdl = eng.attn_pdl
     eng.pos.copy_(torch.tensor([POS, POS % S, min(POS + 1, S)], dtype=torch.int32))
     flags = NV.GEMV_PDL if (pdl and apdl) else 0
     cfg = model.config
@@ -73,4 +75,4 @@ for pdl, apdl in ((True, os.environ.get("PROBE_APDL", "0") == "1"),):
         return f
 
     parts = {sp: timed_graph(seq(sp)) for sp in os.environ.get("PROBE_SEQS", "q,A,p,f,d,qpfd,qApfd").split(",")}
-    print(f"cfg={os.environ.get('LLB200_GEMV_CFG', 'default')} PDL={pdl} attnPDL={apdl}: full {timed_graph(eng._run_step):7.1f} | " + " ".join(f"{k}={v:.0f}" for k, v in parts.items()), flush=True)
+    print(f"cfg={os.environ.get('LLB200_GEMV_CFG', 'default')} PDL={pdl} parity={eng.parity} attnPDL={apdl}: full {timed_graph(eng._run_step):7.1f} | " + " ".join(f"{k}={v:.0f}" for k, v in parts.items()), flush=True)
