@@ -178,6 +178,17 @@ LL_API size_t ll_int4_gemm_tc_scratch_bytes(int M, int N, int K);
 LL_API int ll_int4_gemm_tc(const uint8_t* w_stream, const void* x, const void* bias, void* y, float* scratch, int M, int N,
                            int K, int group, ll_stream stream);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same arithmetic, arguments and result
+ * as ll_int4_gemm_tc, but the split-K partial sums go to an array built into the library
+ * (LL_INT4_GEMM_TC_STATIC_SCRATCH_BYTES per GPU, held until exit); the call allocates nothing.  Shapes whose
+ * ll_int4_gemm_tc_scratch_bytes() exceeds that maximum return LL_ERR_UNSUPPORTED (every 7B layer up to M = 128 fits
+ * except the 32000-column head above M = 64).  All calls on a device share the array: calls that overlap on the GPU
+ * race; calls ordered on one stream do not (nothing in the array has to start at zero). */
+#define LL_INT4_GEMM_TC_STATIC_SCRATCH_BYTES (32u << 20)
+LL_API int ll_int4_gemm_tc_static(const uint8_t* w_stream, const void* x, const void* bias, void* y, int M, int N, int K,
+                                  int group, ll_stream stream);
+
 /* ---------------------------------------------------------------------------------------
  * llm.int8 (ref: Linear8bitLt, quantization.py:36-75; arithmetic = bitsandbytes double_quant / MatMul8bitLt,
  * un-vendored in the reference, restated from arXiv:2208.07339 - see oracle/quant.py).

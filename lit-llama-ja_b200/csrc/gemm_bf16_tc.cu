@@ -694,3 +694,62 @@ int ll_int4_gemm_tc(const uint8_t* w_stream, const void* x, const void* bias, vo
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// No-allocation variant of ll_int4_gemm_tc (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+// The split-K partial sums live in a file-scope device array instead of a caller-provided buffer.  Every GPU that loads
+// this library holds LL_INT4_GEMM_TC_STATIC_SCRATCH_BYTES until exit.  All calls on a device share the array: two calls
+// that overlap on the GPU (different streams, or graphs replayed concurrently) race on it.  Nothing in it has to start at
+// zero: every (tile, k-split) unit writes rows m < M of its block of partial sums, and w4_reduce_kernel (after it on
+// the stream) reads exactly those rows, so the previous call's contents are never observed.
+// ---------------------------------------------------------------------------------------------------------------------
+static_assert(!llb::W4_REDUCE_IN_KERNEL, "the static-scratch entry point has no arrival counters: it needs the two-kernel reduce");
+static __device__ __align__(256) float g_w4_static_scratch[LL_INT4_GEMM_TC_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+namespace {
+// In host code `g_w4_static_scratch` is only a stand-in for the symbol: its device address comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+float* w4_static_scratch(void) {
+  constexpr int MAX_DEV = 64;
+  static float* ptr[MAX_DEV] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= MAX_DEV) {
+    set_error("ll_int4_gemm_tc_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return nullptr;
+  }
+  if (ptr[dev] == nullptr) {
+    void* d = nullptr;
+    e = cudaGetSymbolAddress(&d, g_w4_static_scratch);
+    if (e != cudaSuccess || d == nullptr) {
+      set_error("ll_int4_gemm_tc_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return nullptr;
+    }
+    ptr[dev] = static_cast<float*>(d);
+  }
+  return ptr[dev];
+}
+}  // namespace
+
+extern "C" int ll_int4_gemm_tc_static(const uint8_t* w_stream, const void* x, const void* bias, void* y, int M, int N, int K,
+                                      int group, ll_stream stream) {
+  LL_CHECK_ARG(w_stream && x && y, "null pointer");
+  LL_CHECK_ARG(M >= 1 && M <= 128, "ll_int4_gemm_tc_static serves 1 <= M <= 128 rows (got %d)", M);
+  if (N <= 0 || K <= 0 || group <= 0 || N % llb::W4_BN != 0 || group % llb::W4_KB != 0 || K % group != 0) {
+    set_error("ll_int4_gemm_tc_static needs N %% 128 == 0 and group %% 128 == 0 (N=%d K=%d group=%d)", N, K, group);
+    return LL_ERR_UNSUPPORTED;
+  }
+  const size_t need = ll_int4_gemm_tc_scratch_bytes(M, N, K);
+  if (need > (size_t)LL_INT4_GEMM_TC_STATIC_SCRATCH_BYTES) {
+    set_error("ll_int4_gemm_tc_static: M=%d N=%d K=%d needs %zu bytes of split-K scratch, the built-in array holds %zu: "
+              "use ll_int4_gemm_tc with a caller-provided buffer", M, N, K, need, (size_t)LL_INT4_GEMM_TC_STATIC_SCRATCH_BYTES);
+    return LL_ERR_UNSUPPORTED;
+  }
+  float* scratch = nullptr;
+  if (need != 0) {
+    scratch = w4_static_scratch();
+    if (scratch == nullptr) return LL_ERR_CUDA;
+  }
+  return ll_int4_gemm_tc(w_stream, x, bias, y, scratch, M, N, K, group, stream);
+}

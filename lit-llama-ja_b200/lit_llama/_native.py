@@ -71,6 +71,7 @@ EXPORTS = {
     "ll_gemm_bf16_tc": ([vp, vp, vp, vp, i32, i32, i32, vp], C.c_int),
     "ll_int4_gemm_tc_scratch_bytes": ([i32, i32, i32], sz_t),
     "ll_int4_gemm_tc": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, vp], C.c_int),
+    "ll_int4_gemm_tc_static": ([vp, vp, vp, vp, i32, i32, i32, i32, vp], C.c_int),
     "ll_int8_quantize_weight": ([vp, i32, vp, vp, i32, i32, vp], C.c_int),
     "ll_int8_workspace_bytes": ([i32, i32, i32], sz_t),
     "ll_int8_linear": ([vp, i32, vp, vp, vp, vp, i32, i32, i32, C.c_float, vp, sz_t, vp], C.c_int),
