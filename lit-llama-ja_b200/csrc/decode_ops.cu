@@ -299,6 +299,262 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
   if (threadIdx.x == 0) counters[bh] = 0;
 }
 
+// ---------------------------------------------------------------- decode attention, K/V staged ahead of the wait
+// The kernel above is latency-bound: after the c_attn GEMV retires it pays position -> K/V rows -> combine as dependent
+// memory round trips (3.2 us of its 9.4 us per layer at position 640, profiles/r02_gemv_experiments.md).  Only ONE row of
+// the layer's cache changes in this step - the slot the c_attn epilogue writes - so everything else can be in shared
+// memory before the producer finishes.  As a programmatic dependent this kernel
+//   1. BEFORE griddepcontrol.wait: reads the position (a guess: the kernel that advanced it may formally still be running),
+//      and one thread issues two bulk-TMA copies - this split's K rows and V rows, contiguous in [head][slot][hs] - into
+//      shared memory: they stream while the c_attn GEMV still runs;
+//   2. AFTER the wait, in one round trip: the true position, q, and the row at the guessed slot (the row c_attn just wrote)
+//      - the latter patches shared memory;
+//   3. if the guess was the true position (always, except when a step starts within microseconds of the position update)
+//      the softmax runs out of shared memory; otherwise the same loop reads global memory (same arithmetic, same bits).
+// One (batch, head) = one cluster of nsplit <= 8 CTAs combining through distributed shared memory, as above.
+template <typename T> struct piece16;
+template <> struct piece16<__nv_bfloat16> {
+  static constexpr int PV = 8;
+  static __device__ __forceinline__ void cvt(const uint4& r, float* o) {
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      o[2 * j] = bf16_bits_to_f32(w[j] & 0xffff);
+      o[2 * j + 1] = bf16_bits_to_f32(w[j] >> 16);
+    }
+  }
+};
+template <> struct piece16<float> {
+  static constexpr int PV = 4;
+  static __device__ __forceinline__ void cvt(const uint4& r, float* o) {
+    o[0] = __uint_as_float(r.x); o[1] = __uint_as_float(r.y); o[2] = __uint_as_float(r.z); o[3] = __uint_as_float(r.w);
+  }
+};
+#define LL_ATTN_FLAG_MISGUESS 0x100  // test hook (ll_decode_attn flags): a wrong position guess -> the global-memory path
+#define LL_ATTN_FLAG_POISON 0x200    // test hook: the staged copy of the producer's row is NaN before it is patched
+
+template <typename T, int HS>
+__global__ void __launch_bounds__(128) decode_attn_pf_kernel(const T* __restrict__ q, const T* __restrict__ kc,
+                                                             const T* __restrict__ vc, const int32_t* __restrict__ pos,
+                                                             T* __restrict__ y, int S, int nsplit, int rows_cap, int use_pdl,
+                                                             unsigned long long* __restrict__ trace) {
+  ATRACE(0);
+  constexpr int EPL = HS / 8, PV = piece16<T>::PV, NP = EPL / PV, PPR = HS / PV, NW = 4, RL = 6;
+  static_assert(EPL % PV == 0, "a lane takes whole 16-byte pieces");
+  extern __shared__ __align__(128) uint8_t dyn[];
+  T* ks = reinterpret_cast<T*>(dyn);
+  T* vs = ks + (size_t)rows_cap * HS;
+  float* s_o = reinterpret_cast<float*>(dyn);  // [NW * 4][HS], aliased onto the K rows once every warp has left the loop
+  __shared__ float s_m[NW * 4], s_l[NW * 4];
+  __shared__ float c_st[8][HS + 2];
+  __shared__ __align__(8) uint64_t bar;
+  const int trig = (use_pdl >> 1) & 3;
+  if (trig == 1 || (use_pdl & 1)) pdl_launch_dependents();
+  const int bh = blockIdx.x, split = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, lg = lane >> 3, li = lane & 7;
+
+  // ---- 1. the guess and the copies
+  int g_nvalid = min(max(__ldcg(pos + 2), 0), S), g_slot = min(max(__ldcg(pos + 1), 0), S - 1);
+  if (use_pdl & LL_ATTN_FLAG_MISGUESS) g_slot = (g_slot + 1) % S;
+  const int gper = (g_nvalid + nsplit - 1) / nsplit;
+  const int gs0 = min(split * gper, g_nvalid), gs1 = min(gs0 + gper, g_nvalid);
+  const int rows = gs1 - gs0;  // <= rows_cap = ceil(S / nsplit)
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    fence_barrier_init();
+    if (rows > 0) {
+      const uint32_t bytes = (uint32_t)rows * HS * (uint32_t)sizeof(T);
+      mbar_expect_tx(&bar, 2 * bytes);
+      bulk_load_1d(ks, kc + ((size_t)bh * S + gs0) * HS, bytes, &bar);
+      bulk_load_1d(vs, vc + ((size_t)bh * S + gs0) * HS, bytes, &bar);
+    }
+  }
+  __syncthreads();
+  if (use_pdl & 1) pdl_wait();
+  ATRACE(1);
+
+  // ---- 2. one round trip: true position, q, the row the producer wrote
+  const int nvalid = min(__ldcg(pos + 2), S), slot = __ldcg(pos + 1);
+  uint4 qraw[NP];
+#pragma unroll
+  for (int j = 0; j < NP; ++j) qraw[j] = __ldcg(reinterpret_cast<const uint4*>(q + (size_t)bh * HS + (j * 8 + li) * PV));
+  const bool fix_mine = g_slot >= gs0 && g_slot < gs1 && threadIdx.x < 2 * PPR;
+  const int fpiece = threadIdx.x < PPR ? threadIdx.x : threadIdx.x - PPR;
+  uint4 fx = make_uint4(0u, 0u, 0u, 0u);
+  if (fix_mine)
+    fx = __ldcg(reinterpret_cast<const uint4*>((threadIdx.x < PPR ? kc : vc) + ((size_t)bh * S + g_slot) * HS + fpiece * PV));
+  const bool ok = nvalid == g_nvalid && slot == g_slot;  // uniform over the cluster
+  if (rows > 0) mbar_wait(&bar, 0);
+  if (fix_mine && (use_pdl & LL_ATTN_FLAG_POISON))
+    *reinterpret_cast<uint4*>((threadIdx.x < PPR ? ks : vs) + (size_t)(g_slot - gs0) * HS + fpiece * PV) =
+        make_uint4(0x7fc07fc0u, 0x7fc07fc0u, 0x7fc07fc0u, 0x7fc07fc0u);
+  if (ok && fix_mine)
+    *reinterpret_cast<uint4*>((threadIdx.x < PPR ? ks : vs) + (size_t)(g_slot - gs0) * HS + fpiece * PV) = fx;
+  __syncthreads();
+
+  const float scale_log2 = rsqrtf((float)HS) * 1.4426950408889634f;
+  float qr[EPL];
+#pragma unroll
+  for (int j = 0; j < NP; ++j) piece16<T>::cvt(qraw[j], qr + j * PV);
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) qr[e] *= scale_log2;
+  const int per = (nvalid + nsplit - 1) / nsplit;
+  const int s0 = min(split * per, nvalid), s1 = min(s0 + per, nvalid);
+  const unsigned gmask = 0xffu << (lg * 8);
+
+  // ---- 3. softmax over this split's rows: RL rows per lane group at a time (scores first, then one rescale)
+  float m = -INFINITY, l = 0.f, o[EPL];
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) o[e] = 0.f;
+  auto run = [&](auto load_piece) {
+    for (int sb = s0 + warp * 4 + lg; sb < s1; sb += 4 * NW * RL) {
+      float sc[RL];
+#pragma unroll
+      for (int r = 0; r < RL; ++r) {
+        const int s = min(sb + r * 4 * NW, s1 - 1);  // clamped rows are read but not used
+        float a = 0.f;
+#pragma unroll
+        for (int j = 0; j < NP; ++j) {
+          float kr[PV];
+          piece16<T>::cvt(load_piece(0, s, j), kr);
+#pragma unroll
+          for (int i = 0; i < PV; ++i) a = fmaf(qr[j * PV + i], kr[i], a);
+        }
+        a += __shfl_xor_sync(gmask, a, 1);
+        a += __shfl_xor_sync(gmask, a, 2);
+        a += __shfl_xor_sync(gmask, a, 4);
+        sc[r] = sb + r * 4 * NW < s1 ? a : -INFINITY;
+      }
+      float mn = m;
+#pragma unroll
+      for (int r = 0; r < RL; ++r) mn = fmaxf(mn, sc[r]);
+      const float corr = exp2f(m - mn);  // sc[0] is finite: mn > -inf
+      l *= corr;
+#pragma unroll
+      for (int e = 0; e < EPL; ++e) o[e] *= corr;
+#pragma unroll
+      for (int r = 0; r < RL; ++r) {
+        const float pr = exp2f(sc[r] - mn);  // 0 for the clamped rows
+        const int s = min(sb + r * 4 * NW, s1 - 1);
+        l += pr;
+#pragma unroll
+        for (int j = 0; j < NP; ++j) {
+          float vr[PV];
+          piece16<T>::cvt(load_piece(1, s, j), vr);
+#pragma unroll
+          for (int i = 0; i < PV; ++i) o[j * PV + i] = fmaf(pr, vr[i], o[j * PV + i]);
+        }
+      }
+      m = mn;
+    }
+  };
+  if (ok) {
+    const uint32_t ku = smem_u32(ks), vu = smem_u32(vs);
+    run([&](int which, int s, int j) {
+      return lds128((which ? vu : ku) + (uint32_t)(((s - s0) * HS + (j * 8 + li) * PV) * (int)sizeof(T)));
+    });
+  } else {
+    run([&](int which, int s, int j) {
+      return __ldcg(reinterpret_cast<const uint4*>((which ? vc : kc) + ((size_t)bh * S + s) * HS + (j * 8 + li) * PV));
+    });
+  }
+  if (trig == 2) pdl_launch_dependents();
+  ATRACE(2);
+  __syncthreads();  // s_o aliases the K rows
+  if (li == 0) { s_m[warp * 4 + lg] = m; s_l[warp * 4 + lg] = l; }
+#pragma unroll
+  for (int j = 0; j < NP; ++j)
+#pragma unroll
+    for (int i = 0; i < PV; ++i) s_o[(warp * 4 + lg) * HS + (j * 8 + li) * PV + i] = o[j * PV + i];
+  __syncthreads();
+  if (threadIdx.x < HS) {
+    float M = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < NW * 4; ++i) M = fmaxf(M, s_m[i]);
+    float L = 0.f, O = 0.f;
+    if (M > -INFINITY) {
+#pragma unroll
+      for (int i = 0; i < NW * 4; ++i) {
+        const float c = exp2f(s_m[i] - M);
+        L += s_l[i] * c;
+        O += s_o[i * HS + threadIdx.x] * c;
+      }
+    }
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(&c_st[split][0])), "r"(0));
+    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote + 4u * (2 + threadIdx.x)), "f"(O) : "memory");
+    if (threadIdx.x == 0) {
+      asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(M) : "memory");
+      asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote + 4u), "f"(L) : "memory");
+    }
+  }
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+  ATRACE(3);
+  if (split != 0) return;
+  if (threadIdx.x < HS) {
+    float M = -INFINITY;
+    for (int i = 0; i < nsplit; ++i) M = fmaxf(M, c_st[i][0]);
+    float L = 0.f, O = 0.f;
+    for (int i = 0; i < nsplit; ++i) {  // split order: deterministic
+      const float mi = c_st[i][0];
+      if (mi > -INFINITY) {
+        const float c = exp2f(mi - M);
+        L += c_st[i][1] * c;
+        O += c_st[i][2 + threadIdx.x] * c;
+      }
+    }
+    dt<T>::st(y + (size_t)bh * HS, threadIdx.x, O / L);
+  }
+}
+
+// The K/V-staging kernel serves the shapes whose split fits shared memory beside a resident GEMV CTA (two attention CTAs
+// of <= 54 KB next to a 116 KB one); LLB200_ATTN_STAGE=0 keeps the direct kernel (A/B measurements).
+constexpr size_t PF_DYN_MAX = 50 * 1024;
+template <typename T, int HS>
+size_t pf_dyn_bytes(int rows_cap) {
+  const size_t kv = (size_t)2 * rows_cap * HS * sizeof(T), so = (size_t)16 * HS * sizeof(float);
+  return kv > so ? kv : so;
+}
+template <typename T, int HS>
+bool pf_ok(int cache_len, int splits) {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("LLB200_ATTN_STAGE");
+    on = (e && atoi(e) == 0) ? 0 : 1;
+  }
+  return on && pf_dyn_bytes<T, HS>((cache_len + splits - 1) / splits) <= PF_DYN_MAX;
+}
+// 1: launched, 0: not for this shape, < 0: error
+template <typename T, int HS>
+int launch_attn_pf(const void* q, const void* k_cache, const void* v_cache, const int32_t* pos, void* y, int cache_len,
+                   int splits, dim3 grid, dim3 block, cudaStream_t st, bool pdl, int kflags, unsigned long long* tr) {
+  if constexpr ((HS / 8) % piece16<T>::PV != 0) {
+    return 0;
+  } else {
+    if (!pf_ok<T, HS>(cache_len, splits)) return 0;
+    const int rows_cap = (cache_len + splits - 1) / splits;
+    const size_t dyn = pf_dyn_bytes<T, HS>(rows_cap);
+    static size_t configured = 0;
+    if (dyn > configured) {
+      if (configured == 0) prefer_max_smem(decode_attn_pf_kernel<T, HS>);
+      LL_CUDA(cudaFuncSetAttribute(decode_attn_pf_kernel<T, HS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+      configured = dyn;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = dyn; cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = (unsigned)splits; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl ? 2 : 1;
+    LL_CUDA(cudaLaunchKernelEx(&cfg, decode_attn_pf_kernel<T, HS>, (const T*)q, (const T*)k_cache, (const T*)v_cache, pos,
+                               (T*)y, cache_len, splits, rows_cap, kflags, tr));
+    return 1;
+  }
+}
+
 // ---------------------------------------------------------------- elementwise
 template <typename T>
 __global__ void silu_mul_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ y, size_t n) {
@@ -442,7 +698,11 @@ int ll_decode_attn(const void* q, const void* k_cache, const void* v_cache, cons
       prefer_max_smem(decode_attn_kernel<TT, HS, true>);                                                          \
       once = true;                                                                                                \
     }                                                                                                             \
-    if (cl) {                                                                                                     \
+    const int pfr = cl ? launch_attn_pf<TT, HS>(q, k_cache, v_cache, pos, y, cache_len, max_splits, grid, block, st, pdl, \
+                                                kflags | (flags & (LL_ATTN_FLAG_MISGUESS | LL_ATTN_FLAG_POISON)), tr) : 0; \
+    if (pfr < 0) return pfr;                                                                                      \
+    if (pfr > 0) {                                                                                                \
+    } else if (cl) {                                                                                              \
       cudaLaunchConfig_t cfg{};                                                                                   \
       cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = 0; cfg.stream = st;                        \
       cudaLaunchAttribute attr[2];                                                                                \

@@ -269,6 +269,96 @@ def test_decode_attention_hs128_vs_float64_softmax(B, S, pos, splits):
     assert np.abs(got - want).max() <= 2.0 ** -8 * np.abs(want).max() + 1e-6, np.abs(got - want).max()
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("B,S,pos,splits", [(1, 768, 0, 8), (1, 768, 5, 8), (1, 768, 95, 8), (1, 768, 96, 8), (1, 768, 97, 8),
+                                            (1, 768, 640, 8), (1, 768, 767, 8), (1, 768, 1000, 8), (8, 768, 700, 8),
+                                            (1, 520, 519, 8), (1, 520, 777, 8), (2, 384, 383, 4), (1, 192, 100, 2)])
+def test_decode_attention_staged_kv_paths_agree(B, S, pos, splits, dtype):
+    """The K/V-staging decode attention (decode_attn_pf_kernel: this split's rows copied to shared memory by bulk TMA ahead
+    of the wait, the producer's row patched in afterwards) against a float64 softmax, and its three routes against each
+    other BIT FOR BIT: staged rows, staged rows with the patched row poisoned first (the patch must repair it), and the
+    global-memory route taken when the position guess was stale (forced by the test flag)."""
+    from lit_llama import _native as NV
+
+    if dtype == torch.float32 and 2 * ((S + splits - 1) // splits) * 128 * 4 > 50 * 1024:
+        pytest.skip("fp32 rows of this split do not fit the staging budget (the direct kernel serves it)")
+    nh, hs = 32, 128
+    g = torch.Generator(device=DEV).manual_seed(B * 100000 + S + pos)
+    q = (torch.randn((B, nh * hs), device=DEV, generator=g)).to(dtype)
+    k = (torch.randn((B, nh, S, hs), device=DEV, generator=g)).to(dtype)
+    v = (torch.randn((B, nh, S, hs), device=DEV, generator=g)).to(dtype)
+    n_valid = min(pos + 1, S)
+    pos3 = torch.tensor([pos, pos % S, n_valid], dtype=torch.int32, device=DEV)
+    scratch = torch.empty(NV.attn_scratch_bytes(B, nh, hs, splits) // 4 + 16, dtype=torch.float32, device=DEV)
+    counters = torch.zeros(B * nh, dtype=torch.int32, device=DEV)
+    outs = []
+    for flags in (0, 0x200, 0x100, 0x300):
+        y = torch.full((B + 2, nh * hs), 7.0, device=DEV, dtype=dtype)
+        NV.call("ll_decode_attn", NV.ptr(q), NV.ptr(k), NV.ptr(v), NV.ptr(pos3), NV.ptr(y[1:]),
+                NV.LL_BF16 if dtype == torch.bfloat16 else NV.LL_F32, B, nh, hs, S, splits,
+                NV.ptr(scratch), NV.ptr(counters), flags, NV.stream())
+        torch.cuda.synchronize()
+        assert (y[0] == 7.0).all() and (y[-1] == 7.0).all()
+        outs.append(y[1:-1].float().cpu().numpy().reshape(B, nh, hs))
+    want = _attn_ref(q.float().cpu().numpy().reshape(B, nh, hs), k.float().cpu().numpy(), v.float().cpu().numpy(), n_valid)
+    tol = (2.0 ** -8 if dtype == torch.bfloat16 else 2.0 ** -18) * np.abs(want).max() + 1e-6
+    assert np.abs(outs[0] - want).max() <= tol, np.abs(outs[0] - want).max()
+    for o in outs[1:]:
+        assert np.array_equal(outs[0], o)
+
+
+@pytest.mark.parametrize("S,pos", [(768, 640), (768, 767), (520, 777)])
+def test_staged_attention_behind_c_attn_as_programmatic_dependent(S, pos):
+    """The race the staging kernel is built around: c_attn (fused RMSNorm, RoPE, K/V row written at the ring slot) followed
+    by the attention kernel as its PROGRAMMATIC DEPENDENT, whose bulk copies of K and V run while c_attn is still computing.
+    The slot's row holds large garbage beforehand, so a result from the stale copy would be far off.  Same bits as the two
+    kernels launched plainly one after the other, over several rounds; the result also matches the float64 softmax."""
+    from lit_llama import _native as NV
+    from oracle import quant as OQ
+
+    E, nh, hs, group, splits = 4096, 32, 128, 128, 8
+    r = np.random.RandomState(S + pos)
+    pk, s, z = _bf16_layer(3 * E, E, group, 26)
+    lin = _stream_of(pk, s, z, 3 * E, E, group, 1)
+    rope_d = torch.from_numpy(OM.build_rope_cache(1024, hs)).to(DEV)
+    nw = torch.from_numpy(OQ.bf16_round((1 + 0.1 * r.randn(E)).astype(np.float32))).to(DEV, torch.bfloat16)
+    x = torch.from_numpy(OQ.bf16_round(r.randn(1, E).astype(np.float32))).to(DEV, torch.bfloat16)
+    g = torch.Generator(device=DEV).manual_seed(pos)
+    k0 = torch.randn((1, nh, S, hs), device=DEV, generator=g).bfloat16()
+    v0 = torch.randn((1, nh, S, hs), device=DEV, generator=g).bfloat16()
+    slot, n_valid = pos % S, min(pos + 1, S)
+    k0[:, :, slot] = 300.0
+    v0[:, :, slot] = -300.0
+    pos3 = torch.tensor([pos, slot, n_valid], dtype=torch.int32, device=DEV)
+    scratch = torch.empty(NV.attn_scratch_bytes(1, nh, hs, splits) // 4 + 16, dtype=torch.float32, device=DEV)
+    counters = torch.zeros(nh, dtype=torch.int32, device=DEV)
+
+    def chain(pdl):
+        kc, vc = k0.clone(), v0.clone()
+        q = torch.zeros((1, E), device=DEV, dtype=torch.bfloat16)
+        y = torch.zeros((1, E), device=DEV, dtype=torch.bfloat16)
+        a = NV.GemvArgs()
+        w, a.stream_kind = lin.stream_for(1)
+        a.w, a.N, a.K, a.group, a.M = w.data_ptr(), 3 * E, E, group, 1
+        a.x, a.y, a.norm_weight, a.eps = x.data_ptr(), q.data_ptr(), nw.data_ptr(), 1e-5
+        a.epilogue, a.flags, a.grid = NV.EPI_ROPE_KV, (NV.GEMV_PDL | NV.GEMV_EVEN) if pdl else 0, 0
+        a.rope, a.pos, a.k_cache, a.v_cache = rope_d.data_ptr(), pos3.data_ptr(), kc.data_ptr(), vc.data_ptr()
+        a.n_head, a.head_size, a.cache_len = nh, hs, S
+        torch.cuda.synchronize()
+        NV.gemv(a)
+        NV.call("ll_decode_attn", NV.ptr(q), NV.ptr(kc), NV.ptr(vc), NV.ptr(pos3), NV.ptr(y), NV.LL_BF16, 1, nh, hs, S, splits,
+                NV.ptr(scratch), NV.ptr(counters), NV.GEMV_PDL if pdl else 0, NV.stream())
+        torch.cuda.synchronize()
+        return y.float().cpu().numpy(), q, kc, vc
+
+    plain, q, kc, vc = chain(False)
+    assert float(kc[:, :, slot].abs().max()) < 100.0, "c_attn did not write the K row"
+    want = _attn_ref(q.float().cpu().numpy().reshape(1, nh, hs), kc.float().cpu().numpy(), vc.float().cpu().numpy(), n_valid)
+    assert np.abs(plain.reshape(1, nh, hs) - want).max() <= 2.0 ** -8 * np.abs(want).max() + 1e-6
+    for _ in range(5):
+        assert np.array_equal(chain(True)[0], plain)
+
+
 def _bf16_layer(N_, K, group, seed):
     from oracle import quant as OQ
 
