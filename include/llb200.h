@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define LL_ABI_VERSION 5
+#define LL_ABI_VERSION 6
 
 #define LL_OK 0
 #define LL_ERR_ARG (-1)         /* bad shape / dtype / null pointer */
@@ -232,10 +232,12 @@ LL_API int ll_sample_topk(const void* logits, int V, float temperature, int top_
  * NVLink peer memory fused with the residual add: x = bf16(x + bf16(sum over ranks of part_r)), summed in rank
  * order on every rank.  peer_parts / peer_flags: HOST arrays of `world` device pointers (symmetric-memory mappings
  * of every rank's partial-sum buffer and int32[world] flag array, zeroed once).  The caller alternates between two
- * partial-sum buffers from call to call.  epoch_counter: local device int32, zero before first use.
- * ------------------------------------------------------------------------------------- */
+ * partial-sum buffers from call to call.  epoch_counter: local device int32[LL_TP_MAX_CTAS], zero before first use.
+ * flags: LL_GEMV_PDL = launch as a link of a programmatic-dependent-launch chain (the next kernel of the stream may start
+ * its prologue while the exchange runs; needs the EVEN / ODD GEMV footprints around it), 0 = plain launch. */
+#define LL_TP_MAX_CTAS 8
 LL_API int ll_tp_allreduce_add(void* x, const uint64_t* peer_parts, const uint64_t* peer_flags, int32_t* epoch_counter, int rank,
-                        int world, int n, ll_stream stream);
+                        int world, int n, int flags, ll_stream stream);
 /* Second half of the pushed exchange (LL_EPI_PUSH): wait until `arrivals` more CTAs have signalled the counter of the
  * current buffer (cnt[j], j alternating 0, 1 from call to call), then x = bf16(x + bf16(sum_r recv[j][r])) from LOCAL
  * memory, rank order.  recv: [2][world][n] bf16 in this rank's symmetric memory; cnt: uint32[2], zero before first use. */

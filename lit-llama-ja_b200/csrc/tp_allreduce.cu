@@ -35,19 +35,29 @@ __device__ __forceinline__ uint4 ld_relaxed_sys_v4(const void* p) {
 }
 
 __global__ void __launch_bounds__(1024) tp_allreduce_add_kernel(const __grid_constant__ TpArgs a, __nv_bfloat16* __restrict__ x,
-                                                                int32_t* __restrict__ epoch_counter, int rank, int world, int n) {
+                                                                int32_t* __restrict__ epoch_counter, int rank, int world, int n,
+                                                                int use_pdl) {
   __shared__ int s_epoch;
-  if (threadIdx.x == 0) s_epoch = ++(*epoch_counter);  // same call count on every rank -> same epoch
-  // (A plain launch on purpose.  Measured on 2 GPUs, 65B: launching this kernel with the programmatic attribute and
-  // triggering the next GEMV early cost 8.70 -> 9.31 ms per token, like every other early launch behind a small
-  // kernel in this chain - profiles/r01_step_probe.md.)
+  // use_pdl (round 2): a link of the programmatic-launch chain.  Round 1 launched this kernel plainly because an early
+  // launch behind it cost time - the cause was CTA placement (a 148-CTA GEMV grid released while a fat CTA holds an SM
+  // doubles up elsewhere, profiles/r02_gemv_experiments.md section 6), cured by the EVEN / ODD GEMV footprints.  With them
+  // the next GEMV's CTAs can start (barriers, norm weights, ring fill from HBM) while the flags and partial sums travel,
+  // and this kernel's own launch latency hides behind the row-parallel GEMV.  Everything that touches data comes after
+  // the wait.
+  if (use_pdl) {
+    pdl_launch_dependents();
+    pdl_wait();
+  }
+  // every CTA counts its own calls (epoch_counter[blockIdx.x]): same call count on every rank and CTA -> same epoch
+  if (threadIdx.x == 0) s_epoch = ++epoch_counter[blockIdx.x];
   // the local residual vector does not depend on the peers: fetched while the flags travel
+  const int first = (blockIdx.x * blockDim.x + threadIdx.x) * 8, stride = gridDim.x * blockDim.x * 8;
   uint4 x_first = make_uint4(0u, 0u, 0u, 0u);
-  if (threadIdx.x * 8 < n) x_first = *reinterpret_cast<const uint4*>(x + threadIdx.x * 8);
+  if (first < n) x_first = *reinterpret_cast<const uint4*>(x + first);
   __syncthreads();
   const int epoch = s_epoch;
-  // announce: "my partial sums of this epoch are in my buffer" (written by the previous kernel of this stream)
-  if (threadIdx.x < world) st_release_sys(a.flags[threadIdx.x] + rank, epoch);
+  // announce (first CTA): "my partial sums of this epoch are in my buffer" (written by the previous kernel of this stream)
+  if (blockIdx.x == 0 && threadIdx.x < world) st_release_sys(a.flags[threadIdx.x] + rank, epoch);
   // wait for every rank's announcement
   if (threadIdx.x < world) {
     const int32_t* f = a.flags[rank] + threadIdx.x;
@@ -55,7 +65,7 @@ __global__ void __launch_bounds__(1024) tp_allreduce_add_kernel(const __grid_con
     }
   }
   __syncthreads();
-  for (int i = threadIdx.x * 8; i < n; i += blockDim.x * 8) {
+  for (int i = first; i < n; i += stride) {
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     // all peers' vectors are requested before any is used: one NVLink round trip, not `world` of them
     for (int r0 = 0; r0 < world; r0 += 8) {
@@ -75,7 +85,7 @@ __global__ void __launch_bounds__(1024) tp_allreduce_add_kernel(const __grid_con
         }
       }
     }
-    const uint4 xv = i == threadIdx.x * 8 ? x_first : *reinterpret_cast<const uint4*>(x + i);
+    const uint4 xv = i == first ? x_first : *reinterpret_cast<const uint4*>(x + i);
     const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
     uint32_t o[4];
 #pragma unroll
@@ -154,7 +164,7 @@ using namespace llb;
 extern "C" {
 
 int ll_tp_allreduce_add(void* x, const uint64_t* peer_parts /* host: world pointers */, const uint64_t* peer_flags /* host */,
-                        int32_t* epoch_counter, int rank, int world, int n, ll_stream stream) {
+                        int32_t* epoch_counter, int rank, int world, int n, int flags, ll_stream stream) {
   LL_CHECK_ARG(x && peer_parts && peer_flags && epoch_counter, "null pointer");
   LL_CHECK_ARG(world >= 2 && world <= MAX_WORLD && rank >= 0 && rank < world, "bad rank/world (%d/%d)", rank, world);
   LL_CHECK_ARG(n > 0 && n % 8 == 0 && ((uintptr_t)x & 15) == 0, "n must be a multiple of 8 and x 16-byte aligned");
@@ -170,8 +180,17 @@ int ll_tp_allreduce_add(void* x, const uint64_t* peer_parts /* host: world point
     prefer_max_smem(tp_allreduce_add_kernel);
     once = true;
   }
-  tp_allreduce_add_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(a, (__nv_bfloat16*)x, epoch_counter, rank, world, n);
-  LL_LAUNCH_OK("tp_allreduce_add_kernel");
+  const bool pdl = (flags & LL_GEMV_PDL) != 0;
+  // as a link of the programmatic chain the CTAs are kept small (256 threads each, one 16-byte piece per thread, up to
+  // LL_TP_MAX_CTAS of them: each must fit beside a resident GEMV CTA to start early, and every piece's peer loads must be
+  // in flight at once - one NVLink round trip); launched plainly it is one CTA of 1024 threads
+  int ctas = 1;
+  if (pdl) {
+    ctas = (n / 8 + 255) / 256;
+    if (ctas > LL_TP_MAX_CTAS) ctas = LL_TP_MAX_CTAS;
+  }
+  LL_CUDA(launch(tp_allreduce_add_kernel, dim3(ctas), dim3(pdl ? 256 : 1024), 0, (cudaStream_t)stream, pdl, a, (__nv_bfloat16*)x,
+                 epoch_counter, rank, world, n, pdl ? 1 : 0));
   return LL_OK;
 }
 

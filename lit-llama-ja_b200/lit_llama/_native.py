@@ -78,7 +78,7 @@ EXPORTS = {
     "ll_gptq_block": ([vp, i32, vp, i32, vp, vp, i32, vp, i32, vp, vp, i32, i32, i32, i32, i32, vp], C.c_int),
     "ll_sample_topk": ([vp, i32, C.c_float, i32, vp, vp, vp, vp, vp, vp], C.c_int),
     "ll_tp_reduce_add": ([vp, vp, vp, vp, i32, i32, i32, vp], C.c_int),
-    "ll_tp_allreduce_add": ([vp, vp, vp, vp, i32, i32, i32, vp], C.c_int),
+    "ll_tp_allreduce_add": ([vp, vp, vp, vp, i32, i32, i32, i32, vp], C.c_int),
     "ll_rmsnorm": ([vp, vp, vp, i32, i32, i32, C.c_float, vp], C.c_int),
     "ll_embed_ssq": ([vp, vp, vp, vp, i32, i32, vp], C.c_int),
     "ll_rope_kv_append": ([vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp], C.c_int),
@@ -92,7 +92,7 @@ EXPORTS = {
 }
 _fn = {name: _proto(name, a, r) for name, (a, r) in EXPORTS.items()}
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 if _fn["ll_abi_version"]() != ABI_VERSION:
     raise ImportError("libllb200.so ABI version mismatch; rebuild with lit-llama-ja_b200/build.py")
 

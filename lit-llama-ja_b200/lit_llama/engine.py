@@ -95,20 +95,24 @@ class DecodeEngine:
         # same GEMV can never share an SM; the attention kernel can then be a programmatic dependent too
         # (measured, profiles/r02_gemv_experiments.md section 6: every SM then holds exactly one CTA of each GEMV and the
         # 7B step drops 1360 -> 1339 us).  Default: on where every Linear of the chain takes the integer-MMA kernel (the
-        # only one with the two footprints) on one GPU; off under tensor parallelism, where the plainly launched
-        # all-reduce kernels already separate the GEMVs.
+        # only one with the two footprints) on one GPU, and under tensor parallelism when the exchange kernel joins
+        # the programmatic chain (below); with a plainly launched exchange kernel the GEMVs are separated anyway.
         lins = [model.lm_head]
         for blk in model.transformer.h:
             lins += [blk.attn.c_attn, _unwrap(blk.attn.c_proj)[0], blk.mlp.c_fc1, blk.mlp.c_fc2, _unwrap(blk.mlp.c_proj)[0]]
         all_u8 = all(lin.stream_for(B)[1] == N.STREAM_U8 for lin in lins)
-        self.parity = _env_flag("LLB200_GEMV_PARITY", not self.tp) and self.use_pdl and all_u8
+        # tensor parallel: the exchange kernel is itself a link of the programmatic chain (LLB200_TP_PDL, default on with the
+        # peer exchange) - the footprints are then needed for the same placement reason
+        self.tp_pdl = (self.tp and self.use_pdl and all_u8 and os.environ.get("LLB200_TP_EXCHANGE", "peer") == "peer"
+                       and _env_flag("LLB200_TP_PDL", True))
+        self.parity = _env_flag("LLB200_GEMV_PARITY", (not self.tp) or self.tp_pdl) and self.use_pdl and all_u8
+        self.tp_pdl = self.tp_pdl and self.parity
         self.attn_pdl = _env_flag("LLB200_PDL_ATTN", self.parity)
         self.n_launches = 0
         self.n_replays = 0
 
         nh, hs = self.nh, cfg.head_size
         self.splits = max(1, min(8, (2 * N._fn["ll_sm_count"]()) // max(1, B * nh), (max_seq_length + 63) // 64))   # <= 8: one cluster per head
-        import os
         if os.environ.get("LLB200_ATTN_SPLITS"):
             self.splits = int(os.environ["LLB200_ATTN_SPLITS"])
         self.attn_scratch = torch.empty(N.attn_scratch_bytes(B, nh, hs, self.splits) // 4 + 16, dtype=f32, device=dev)
@@ -242,7 +246,7 @@ class DecodeEngine:
             self._arrivals = [0, 0]
             self._symm = (recv, cnt, hb, hc)
             self.recv, self.cnt = recv, cnt
-            self.epoch = torch.zeros(1, dtype=torch.int32, device=dev)
+            self.epoch = torch.zeros(8, dtype=torch.int32, device=dev)   # one call counter per exchange CTA (LL_TP_MAX_CTAS)
             self.exchange = "push"
             return
         if mode == "peer":
@@ -261,7 +265,7 @@ class DecodeEngine:
             self._peer_flags = (C.c_uint64 * world)(*[int(p) for p in hf.buffer_ptrs])
             self._symm = (buf, flg, hb, hf)
             self.parts = [buf[0], buf[1]]
-            self.epoch = torch.zeros(1, dtype=torch.int32, device=dev)
+            self.epoch = torch.zeros(8, dtype=torch.int32, device=dev)   # one call counter per exchange CTA (LL_TP_MAX_CTAS)
             self.exchange = "peer"
         elif mode == "nccl":
             self.parts = [self.part, self.part]
@@ -278,7 +282,7 @@ class DecodeEngine:
         elif self.exchange == "peer":
             import ctypes as C
             N.call("ll_tp_allreduce_add", N.ptr(self.x), C.cast(self._peer_parts[j], C.c_void_p), C.cast(self._peer_flags, C.c_void_p),
-                   N.ptr(self.epoch), self.rank, self.world, self.x.numel(), N.stream())
+                   N.ptr(self.epoch), self.rank, self.world, self.x.numel(), N.GEMV_PDL if self.tp_pdl else 0, N.stream())
         else:
             dist.all_reduce(self.part, op=dist.ReduceOp.SUM, group=self.tp_group)
             N.call("ll_add", N.ptr(self.x), N.ptr(self.part), N.ptr(self.x), N.LL_BF16, self.x.numel(), N.stream())

@@ -41,7 +41,8 @@ if mode == "peer":
     torch.cuda.synchronize()
     dist.barrier()
     log("symmetric memory ready")
-    epoch = torch.zeros(1, dtype=torch.int32, device=dev)
+    epoch = torch.zeros(8, dtype=torch.int32, device=dev)
+    FL = 1 if os.environ.get("TP_CHECK_PDL") == "1" else 0    # the exchange kernel as a programmatic-launch link (4 CTAs at n = 8192)
     flags = (C.c_uint64 * world)(*[int(p) for p in hf.buffer_ptrs])
     parts = [(C.c_uint64 * world)(*[int(p) + j * n * 2 for p in hb.buffer_ptrs]) for j in range(2)]
     gen = torch.Generator().manual_seed(5)
@@ -52,19 +53,19 @@ if mode == "peer":
     for it in range(6):
         buf[it & 1].copy_(allp[it, rank])
         N.call("ll_tp_allreduce_add", N.ptr(x), C.cast(parts[it & 1], C.c_void_p), C.cast(flags, C.c_void_p), N.ptr(epoch),
-               rank, world, n, N.stream())
+               rank, world, n, FL, N.stream())
         s = torch.zeros(n)
         for r in range(world):
             s += allp[it, r].float()
         want = (want.float() + s.bfloat16().float()).bfloat16()
     torch.cuda.synchronize()
-    log("all-reduce kernel bit-exact vs host sum:", bool(torch.equal(x.cpu(), want)), "epoch", int(epoch.item()))
+    log("all-reduce kernel bit-exact vs host sum:", bool(torch.equal(x.cpu(), want)), "epoch", int(epoch[0].item()))
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     dist.barrier()
     ev[0].record()
     for it in range(200):
         N.call("ll_tp_allreduce_add", N.ptr(x), C.cast(parts[it & 1], C.c_void_p), C.cast(flags, C.c_void_p), N.ptr(epoch),
-               rank, world, n, N.stream())
+               rank, world, n, FL, N.stream())
     ev[1].record()
     torch.cuda.synchronize()
     log(f"all-reduce+add of {n} bf16: {ev[0].elapsed_time(ev[1]) / 200 * 1e3:.2f} us per call (back-to-back launches)")
