@@ -358,7 +358,8 @@ def main():
             if os.environ.get("LLB200_BENCH_CPU", "1") != "0":     # (profiling runs skip the host leg)
                 out["cpu_baseline"] = cpu_baseline(prefill_sample=64, decode_tokens=1)
     else:
-        out["comm"] = {"collective": "tp_allreduce_add_kernel (peer pull over NVLink, in the step's CUDA graph)",
+        out["comm"] = {"collective": "tp_ll_allreduce_add_kernel (one NVLink traversal: {word, epoch} units pushed into every peer's "
+                                     "receive buffer, summed from local memory; a programmatic-launch link inside the step's CUDA graph)",
                        "exchanges_per_token": 2 * model.config.n_layer, "bytes_per_exchange": model.config.n_embd * 2,
                        "prefill": "NCCL all_reduce (module path)"}
         extra = {"replicas_tokens_per_s": replica}

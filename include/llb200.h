@@ -238,6 +238,14 @@ LL_API int ll_sample_topk(const void* logits, int V, float temperature, int top_
 #define LL_TP_MAX_CTAS 8
 LL_API int ll_tp_allreduce_add(void* x, const uint64_t* peer_parts, const uint64_t* peer_flags, int32_t* epoch_counter, int rank,
                         int world, int n, int flags, ll_stream stream);
+/* The same exchange in ONE NVLink traversal: every rank pushes its partial sums `part` ([n] bf16, local) into every peer's
+ * receive buffer as 16-byte {word, epoch, word, epoch} units (data and flag in one store, NCCL-LL style) and reads the
+ * peers' units from its own memory.  peer_recv: HOST array of `world` device pointers - the symmetric-memory mappings of
+ * every rank's receive buffer of ll_tp_ll_recv_bytes(world, n) bytes, zeroed once.  epoch_counter, flags: as above.
+ * Same result bits as ll_tp_allreduce_add (rank-order fp32 sum, one bf16 rounding, residual add). */
+LL_API size_t ll_tp_ll_recv_bytes(int world, int n);
+LL_API int ll_tp_ll_allreduce_add(void* x, const void* part, const uint64_t* peer_recv, int32_t* epoch_counter, int rank, int world,
+                           int n, int flags, ll_stream stream);
 /* Second half of the pushed exchange (LL_EPI_PUSH): wait until `arrivals` more CTAs have signalled the counter of the
  * current buffer (cnt[j], j alternating 0, 1 from call to call), then x = bf16(x + bf16(sum_r recv[j][r])) from LOCAL
  * memory, rank order.  recv: [2][world][n] bf16 in this rank's symmetric memory; cnt: uint32[2], zero before first use. */

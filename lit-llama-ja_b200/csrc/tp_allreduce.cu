@@ -156,6 +156,115 @@ __global__ void __launch_bounds__(1024) tp_reduce_add_kernel(__nv_bfloat16* __re
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// The exchange in ONE NVLink traversal ("LL": data and flag travel in the same 16-byte store, as in NCCL's low-latency
+// protocol).  The pull kernel above costs three traversals per exchange (flag out, request out, data back); here every
+// rank PUSHES its partial sums into every peer's receive buffer as {word, epoch, word, epoch} units - a 16-byte store
+// carries two payload words and the epoch twice, so a unit whose two epochs both match has arrived whole, whatever the
+// order the fabric delivered the stores in - and then reads the peers' units out of its OWN memory, spinning on the
+// epochs.  No flag array, no fence, no release / acquire pair.  Receive buffers alternate with the epoch's parity: a
+// peer can only send epoch e + 2 after it has received this rank's epoch e + 1, which this rank sends only after the
+// kernel that consumed epoch e has completed (stream order), so a unit is never overwritten before it was read.
+// Sums in rank order (fp32), one bf16 rounding, residual add: identical bits on every rank.
+struct TpLLArgs {
+  uint8_t* recv[MAX_WORLD];  // peer-mapped receive buffers: [2 parities][world senders][n / 8 pieces][32 bytes]
+};
+__device__ __forceinline__ void st_ll(uint8_t* p, uint32_t a, uint32_t b, uint32_t flag) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(flag), "r"(b), "r"(flag) : "memory");
+}
+__device__ __forceinline__ uint4 ld_ll(const uint8_t* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+
+template <int WORLD>  // 0: any world size (loop), else unrolled: all peers' units are requested before any is examined
+__global__ void __launch_bounds__(256) tp_ll_allreduce_add_kernel(const __grid_constant__ TpLLArgs a,
+                                                                  const __nv_bfloat16* __restrict__ part,
+                                                                  __nv_bfloat16* __restrict__ x, int32_t* __restrict__ epoch_counter,
+                                                                  int rank, int world_rt, int n, int use_pdl) {
+  const int world = WORLD > 0 ? WORLD : world_rt;
+  __shared__ int s_epoch;
+  if (use_pdl) {
+    pdl_launch_dependents();
+    pdl_wait();
+  }
+  if (threadIdx.x == 0) s_epoch = ++epoch_counter[blockIdx.x];
+  __syncthreads();
+  const uint32_t epoch = (uint32_t)s_epoch;
+  const int npieces = n >> 3;
+  const size_t lane_bytes = (size_t)npieces * 32;
+  const size_t half = (size_t)(epoch & 1u) * world * lane_bytes;
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < npieces; p += gridDim.x * blockDim.x) {
+    const uint4 mine = __ldcg(reinterpret_cast<const uint4*>(part) + p);
+    const uint4 xv = *(reinterpret_cast<const uint4*>(x) + p);
+    // send to every peer
+    const size_t out_off = half + (size_t)rank * lane_bytes + (size_t)p * 32;
+    for (int r = 0; r < world; ++r) {
+      if (r == rank) continue;
+      st_ll(a.recv[r] + out_off, mine.x, mine.y, epoch);
+      st_ll(a.recv[r] + out_off + 16, mine.z, mine.w, epoch);
+    }
+    // receive: spin until every peer's unit of this epoch is whole
+    const uint8_t* in = a.recv[rank] + half + (size_t)p * 32;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    auto add = [&](uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
+      const uint32_t w[4] = {w0, w1, w2, w3};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        acc[2 * e] += bf16_bits_to_f32(w[e] & 0xffffu);
+        acc[2 * e + 1] += bf16_bits_to_f32(w[e] >> 16);
+      }
+    };
+    if constexpr (WORLD > 0) {
+      uint4 lo[WORLD], hi[WORLD];
+      bool all;
+      do {
+        all = true;
+#pragma unroll
+        for (int r = 0; r < WORLD; ++r) {
+          if (r == rank) continue;
+          lo[r] = ld_ll(in + (size_t)r * lane_bytes);
+          hi[r] = ld_ll(in + (size_t)r * lane_bytes + 16);
+        }
+#pragma unroll
+        for (int r = 0; r < WORLD; ++r) {
+          if (r == rank) continue;
+          all = all && lo[r].y == epoch && lo[r].w == epoch && hi[r].y == epoch && hi[r].w == epoch;
+        }
+      } while (!all);
+#pragma unroll
+      for (int r = 0; r < WORLD; ++r) {  // rank order
+        if (r == rank) add(mine.x, mine.y, mine.z, mine.w);
+        else add(lo[r].x, lo[r].z, hi[r].x, hi[r].z);
+      }
+    } else {
+      for (int r = 0; r < world; ++r) {
+        if (r == rank) {
+          add(mine.x, mine.y, mine.z, mine.w);
+          continue;
+        }
+        uint4 lo, hi;
+        do {
+          lo = ld_ll(in + (size_t)r * lane_bytes);
+          hi = ld_ll(in + (size_t)r * lane_bytes + 16);
+        } while (!(lo.y == epoch && lo.w == epoch && hi.y == epoch && hi.w == epoch));
+        add(lo.x, lo.z, hi.x, hi.z);
+      }
+    }
+    const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float h0 = bf16r(acc[2 * e]), h1 = bf16r(acc[2 * e + 1]);
+      const uint32_t l = f32_to_bf16_bits(__fadd_rn(bf16_bits_to_f32(xw[e] & 0xffffu), h0));
+      const uint32_t h = f32_to_bf16_bits(__fadd_rn(bf16_bits_to_f32(xw[e] >> 16), h1));
+      o[e] = l | (h << 16);
+    }
+    *(reinterpret_cast<uint4*>(x) + p) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
 }  // namespace
 }  // namespace llb
 
@@ -191,6 +300,35 @@ int ll_tp_allreduce_add(void* x, const uint64_t* peer_parts /* host: world point
   }
   LL_CUDA(launch(tp_allreduce_add_kernel, dim3(ctas), dim3(pdl ? 256 : 1024), 0, (cudaStream_t)stream, pdl, a, (__nv_bfloat16*)x,
                  epoch_counter, rank, world, n, pdl ? 1 : 0));
+  return LL_OK;
+}
+
+size_t ll_tp_ll_recv_bytes(int world, int n) { return world > 0 && n > 0 ? (size_t)2 * world * (n / 8) * 32 : 0; }
+
+int ll_tp_ll_allreduce_add(void* x, const void* part, const uint64_t* peer_recv /* host: world pointers */, int32_t* epoch_counter,
+                           int rank, int world, int n, int flags, ll_stream stream) {
+  LL_CHECK_ARG(x && part && peer_recv && epoch_counter, "null pointer");
+  LL_CHECK_ARG(world >= 2 && world <= MAX_WORLD && rank >= 0 && rank < world, "bad rank/world (%d/%d)", rank, world);
+  LL_CHECK_ARG(n > 0 && n % 8 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)part & 15) == 0, "n must be a multiple of 8, x / part 16-byte aligned");
+  TpLLArgs a;
+  memset(&a, 0, sizeof(a));
+  for (int r = 0; r < world; ++r) {
+    LL_CHECK_ARG(peer_recv[r] != 0 && (peer_recv[r] & 15) == 0, "bad receive buffer pointer for rank %d", r);
+    a.recv[r] = (uint8_t*)(uintptr_t)peer_recv[r];
+  }
+  const bool pdl = (flags & LL_GEMV_PDL) != 0;
+  int ctas = (n / 8 + 255) / 256;
+  if (ctas > LL_TP_MAX_CTAS) ctas = LL_TP_MAX_CTAS;
+  cudaStream_t st = (cudaStream_t)stream;
+  const __nv_bfloat16* pp = (const __nv_bfloat16*)part;
+  __nv_bfloat16* xx = (__nv_bfloat16*)x;
+#define LL_TP_WORLD(W) \
+  LL_CUDA(launch(tp_ll_allreduce_add_kernel<W>, dim3(ctas), dim3(256), 0, st, pdl, a, pp, xx, epoch_counter, rank, world, n, pdl ? 1 : 0))
+  if (world == 2) LL_TP_WORLD(2);
+  else if (world == 4) LL_TP_WORLD(4);
+  else if (world == 8) LL_TP_WORLD(8);
+  else LL_TP_WORLD(0);
+#undef LL_TP_WORLD
   return LL_OK;
 }
 

@@ -79,6 +79,8 @@ EXPORTS = {
     "ll_sample_topk": ([vp, i32, C.c_float, i32, vp, vp, vp, vp, vp, vp], C.c_int),
     "ll_tp_reduce_add": ([vp, vp, vp, vp, i32, i32, i32, vp], C.c_int),
     "ll_tp_allreduce_add": ([vp, vp, vp, vp, i32, i32, i32, i32, vp], C.c_int),
+    "ll_tp_ll_recv_bytes": ([i32, i32], sz_t),
+    "ll_tp_ll_allreduce_add": ([vp, vp, vp, vp, i32, i32, i32, i32, vp], C.c_int),
     "ll_rmsnorm": ([vp, vp, vp, i32, i32, i32, C.c_float, vp], C.c_int),
     "ll_embed_ssq": ([vp, vp, vp, vp, i32, i32, vp], C.c_int),
     "ll_rope_kv_append": ([vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp], C.c_int),

@@ -103,7 +103,7 @@ class DecodeEngine:
         all_u8 = all(lin.stream_for(B)[1] == N.STREAM_U8 for lin in lins)
         # tensor parallel: the exchange kernel is itself a link of the programmatic chain (LLB200_TP_PDL, default on with the
         # peer exchange) - the footprints are then needed for the same placement reason
-        self.tp_pdl = (self.tp and self.use_pdl and all_u8 and os.environ.get("LLB200_TP_EXCHANGE", "peer") == "peer"
+        self.tp_pdl = (self.tp and self.use_pdl and all_u8 and os.environ.get("LLB200_TP_EXCHANGE", "ll") in ("peer", "ll")
                        and _env_flag("LLB200_TP_PDL", True))
         self.parity = _env_flag("LLB200_GEMV_PARITY", (not self.tp) or self.tp_pdl) and self.use_pdl and all_u8
         self.tp_pdl = self.tp_pdl and self.parity
@@ -227,7 +227,25 @@ class DecodeEngine:
         B, E = self.x.shape
         rank, world, group = self.model._tp
         self.rank, self.world = rank, world
-        mode = os.environ.get("LLB200_TP_EXCHANGE", "peer")
+        mode = os.environ.get("LLB200_TP_EXCHANGE", "ll")
+        if mode == "ll":
+            # one NVLink traversal per exchange: every rank pushes {word, epoch} units into every peer's receive buffer and
+            # reads the peers' units from its own memory (csrc/tp_allreduce.cu tp_ll_allreduce_add_kernel)
+            import ctypes as C
+            import torch.distributed._symmetric_memory as symm
+            grp = group if group is not None else dist.group.WORLD
+            nbytes = N.call_ret("ll_tp_ll_recv_bytes", world, B * E)
+            recv = symm.empty((nbytes,), dtype=torch.uint8, device=dev)
+            recv.zero_()
+            hr = symm.rendezvous(recv, grp)
+            torch.cuda.synchronize()
+            dist.barrier(group=group)                     # every rank's buffer is zero (no epoch matches) before anyone sends
+            self._peer_recv = (C.c_uint64 * world)(*[int(p) for p in hr.buffer_ptrs])
+            self._symm = (recv, hr)
+            self.parts = [torch.zeros((B, E), dtype=torch.bfloat16, device=dev) for _ in range(2)]
+            self.epoch = torch.zeros(8, dtype=torch.int32, device=dev)   # one call counter per exchange CTA (LL_TP_MAX_CTAS)
+            self.exchange = "ll"
+            return
         if mode == "push":
             # the row-parallel GEMV's epilogue stores its partial sums into every rank's receive buffer and counts
             # its CTAs in; ll_tp_reduce_add then sums from local memory (csrc/gemv_int4.cu LL_EPI_PUSH, tp_allreduce.cu)
@@ -272,13 +290,17 @@ class DecodeEngine:
             self.exchange = "nccl"
             self.use_graph = False
         else:
-            raise ValueError(f"LLB200_TP_EXCHANGE must be 'push', 'peer' or 'nccl', not {mode!r}")
+            raise ValueError(f"LLB200_TP_EXCHANGE must be 'll', 'peer', 'push' or 'nccl', not {mode!r}")
 
     def _reduce_add(self, j: int):
         """x += sum over ranks of the partial result in buffer ``j``: the path's only exchange step."""
         if self.exchange == "push":
             N.call("ll_tp_reduce_add", N.ptr(self.x), N.ptr(self.recv), N.ptr(self.cnt), N.ptr(self.epoch), self.world,
                    self.x.numel(), self._arrivals[j], N.stream())
+        elif self.exchange == "ll":
+            import ctypes as C
+            N.call("ll_tp_ll_allreduce_add", N.ptr(self.x), N.ptr(self.parts[j]), C.cast(self._peer_recv, C.c_void_p),
+                   N.ptr(self.epoch), self.rank, self.world, self.x.numel(), N.GEMV_PDL if self.tp_pdl else 0, N.stream())
         elif self.exchange == "peer":
             import ctypes as C
             N.call("ll_tp_allreduce_add", N.ptr(self.x), C.cast(self._peer_parts[j], C.c_void_p), C.cast(self._peer_flags, C.c_void_p),

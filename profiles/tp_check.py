@@ -70,6 +70,45 @@ if mode == "peer":
     torch.cuda.synchronize()
     log(f"all-reduce+add of {n} bf16: {ev[0].elapsed_time(ev[1]) / 200 * 1e3:.2f} us per call (back-to-back launches)")
 
+if mode in ("peer", "ll"):
+    # the one-traversal exchange (tp_ll_allreduce_add_kernel) alone: bit-exact against the host's rank-order sum, then timed
+    import ctypes as C
+    import torch.distributed._symmetric_memory as symm
+    from lit_llama import _native as N
+
+    for n in (4096, 8192):
+        nbytes = N.call_ret("ll_tp_ll_recv_bytes", world, n)
+        recv = symm.empty((nbytes,), dtype=torch.uint8, device=dev)
+        recv.zero_()
+        hr = symm.rendezvous(recv, dist.group.WORLD)
+        torch.cuda.synchronize()
+        dist.barrier()
+        peers = (C.c_uint64 * world)(*[int(p) for p in hr.buffer_ptrs])
+        ep = torch.zeros(8, dtype=torch.int32, device=dev)
+        FL2 = 1 if os.environ.get("TP_CHECK_PDL") == "1" else 0
+        gen = torch.Generator().manual_seed(7 + n)
+        x0 = torch.randn(n, generator=gen).bfloat16()
+        allp = torch.randn(7, world, n, generator=gen).bfloat16()
+        x, want = x0.to(dev), x0.clone()
+        part = torch.zeros(n, dtype=torch.bfloat16, device=dev)
+        for it in range(7):
+            part.copy_(allp[it, rank])
+            N.call("ll_tp_ll_allreduce_add", N.ptr(x), N.ptr(part), C.cast(peers, C.c_void_p), N.ptr(ep), rank, world, n, FL2, N.stream())
+            ssum = torch.zeros(n)
+            for r in range(world):
+                ssum += allp[it, r].float()
+            want = (want.float() + ssum.bfloat16().float()).bfloat16()
+        torch.cuda.synchronize()
+        log(f"LL exchange n={n}: bit-exact vs host sum:", bool(torch.equal(x.cpu(), want)))
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        dist.barrier()
+        ev[0].record()
+        for it in range(200):
+            N.call("ll_tp_ll_allreduce_add", N.ptr(x), N.ptr(part), C.cast(peers, C.c_void_p), N.ptr(ep), rank, world, n, FL2, N.stream())
+        ev[1].record()
+        torch.cuda.synchronize()
+        log(f"LL exchange of {n} bf16: {ev[0].elapsed_time(ev[1]) / 200 * 1e3:.2f} us per call (back-to-back launches)")
+
 g = np.load(ROOT / "tests" / "golden" / "model_tiny.npz")
 idx = torch.from_numpy(g["idx"][:1]).to(dev)
 ref_model = TM.build_q_model(g, "rtn32bf16.", torch.bfloat16)
