@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(1024) tp_reduce_add_kernel(__nv_bfloat16* __re
 // kernel that consumed epoch e has completed (stream order), so a unit is never overwritten before it was read.
 // Sums in rank order (fp32), one bf16 rounding, residual add: identical bits on every rank.
 struct TpLLArgs {
-  uint8_t* recv[MAX_WORLD];  // peer-mapped receive buffers: [2 parities][world senders][n / 8 pieces][32 bytes]
+  uint8_t* recv[MAX_WORLD];  // peer-mapped receive buffers: [2 parities][world senders][2 halves][n / 8 pieces][16 bytes]
 };
 __device__ __forceinline__ void st_ll(uint8_t* p, uint32_t a, uint32_t b, uint32_t flag) {
   asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(flag), "r"(b), "r"(flag) : "memory");
@@ -193,20 +193,22 @@ __global__ void __launch_bounds__(256) tp_ll_allreduce_add_kernel(const __grid_c
   __syncthreads();
   const uint32_t epoch = (uint32_t)s_epoch;
   const int npieces = n >> 3;
-  const size_t lane_bytes = (size_t)npieces * 32;
+  // a sender's lane = two arrays of npieces 16-byte units (first / second half of every piece): a warp's store instruction
+  // then covers 512 contiguous bytes - whole 128-byte lines on the fabric instead of half-filled ones
+  const size_t half_bytes = (size_t)npieces * 16, lane_bytes = 2 * half_bytes;
   const size_t half = (size_t)(epoch & 1u) * world * lane_bytes;
   for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < npieces; p += gridDim.x * blockDim.x) {
     const uint4 mine = __ldcg(reinterpret_cast<const uint4*>(part) + p);
     const uint4 xv = *(reinterpret_cast<const uint4*>(x) + p);
     // send to every peer
-    const size_t out_off = half + (size_t)rank * lane_bytes + (size_t)p * 32;
+    const size_t out_off = half + (size_t)rank * lane_bytes + (size_t)p * 16;
     for (int r = 0; r < world; ++r) {
       if (r == rank) continue;
       st_ll(a.recv[r] + out_off, mine.x, mine.y, epoch);
-      st_ll(a.recv[r] + out_off + 16, mine.z, mine.w, epoch);
+      st_ll(a.recv[r] + out_off + half_bytes, mine.z, mine.w, epoch);
     }
     // receive: spin until every peer's unit of this epoch is whole
-    const uint8_t* in = a.recv[rank] + half + (size_t)p * 32;
+    const uint8_t* in = a.recv[rank] + half + (size_t)p * 16;
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     auto add = [&](uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
       const uint32_t w[4] = {w0, w1, w2, w3};
@@ -225,7 +227,7 @@ __global__ void __launch_bounds__(256) tp_ll_allreduce_add_kernel(const __grid_c
         for (int r = 0; r < WORLD; ++r) {
           if (r == rank) continue;
           lo[r] = ld_ll(in + (size_t)r * lane_bytes);
-          hi[r] = ld_ll(in + (size_t)r * lane_bytes + 16);
+          hi[r] = ld_ll(in + (size_t)r * lane_bytes + half_bytes);
         }
 #pragma unroll
         for (int r = 0; r < WORLD; ++r) {
@@ -247,7 +249,7 @@ __global__ void __launch_bounds__(256) tp_ll_allreduce_add_kernel(const __grid_c
         uint4 lo, hi;
         do {
           lo = ld_ll(in + (size_t)r * lane_bytes);
-          hi = ld_ll(in + (size_t)r * lane_bytes + 16);
+          hi = ld_ll(in + (size_t)r * lane_bytes + half_bytes);
         } while (!(lo.y == epoch && lo.w == epoch && hi.y == epoch && hi.w == epoch));
         add(lo.x, lo.z, hi.x, hi.z);
       }
