@@ -59,7 +59,7 @@ def config_dict(n_gpus):
         "prompt_len": PROMPT_LEN, "new_tokens": NEW_TOKENS, "batch": 1,
         "parallelism": "single GPU" if n_gpus == 1 else
         f"tensor-parallel TP{n_gpus}: one sequence over {n_gpus} GPUs (column-parallel c_attn/c_fc1/c_fc2, row-parallel c_proj "
-        f"+ peer all-reduce tp_allreduce_add_kernel over NVLink, KV cache sharded by head)",
+        f"+ one-traversal push exchange tp_ll_allreduce_add_kernel over NVLink, KV cache sharded by head)",
         "l2": "inputs larger than L2 (3.5 GB of weights streamed per token vs 126 MB L2)",
     }
 
