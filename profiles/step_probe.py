@@ -75,4 +75,7 @@ for pdl in (True,):
         return f
 
     parts = {sp: timed_graph(seq(sp)) for sp in os.environ.get("PROBE_SEQS", "q,A,p,f,d,qpfd,qApfd").split(",")}
-    print(f"cfg={os.environ.get('LLB200_GEMV_CFG', 'default')} PDL={pdl} parity={eng.parity} attnPDL={apdl}: full {timed_graph(eng._run_step):7.1f} | " + " ".join(f"{k}={v:.0f}" for k, v in parts.items()), flush=True)
+    import subprocess
+    clk = subprocess.run(["nvidia-smi", "--query-gpu=clocks.sm,clocks.max.sm,power.draw", "--format=csv,noheader", "-i", "0"],
+                         capture_output=True, text=True).stdout.strip()
+    print(f"[{clk}] cfg={os.environ.get('LLB200_GEMV_CFG', 'default')} PDL={pdl} parity={eng.parity} attnPDL={apdl}: full {timed_graph(eng._run_step):7.1f} | " + " ".join(f"{k}={v:.0f}" for k, v in parts.items()), flush=True)
