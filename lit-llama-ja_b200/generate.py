@@ -99,12 +99,19 @@ def generate(
 
 
 def load_model(checkpoint_path: Path, quantize: Optional[str], device: torch.device, dtype: torch.dtype) -> LLaMA:
-    """ref: generate.py:124-136 (lazy_load + quantization ctx + load_state_dict)."""
+    """ref: generate.py:124-136 (lazy_load + quantization ctx + load_state_dict).  GPTQ checkpoints go through the
+    streaming loader (disk -> pinned -> HBM, the GEMV stream of every layer built under the read); llm.int8 quantizes a
+    floating-point checkpoint inside ``load_state_dict``, tensor by tensor, from the lazy placeholders."""
+    from lit_llama.utils import stream_load_state_dict
+
     with lazy_load(checkpoint_path) as checkpoint:
         name = llama_model_lookup(checkpoint)
         with EmptyInitOnDevice(device=device, dtype=dtype, quantization_mode=quantize):
             model = LLaMA.from_name(name)
-        model.load_state_dict(checkpoint)
+        if torch.device(device).type == "cuda" and quantize is not None and quantize.startswith("gptq"):
+            stream_load_state_dict(model, checkpoint_path, strict=True)
+        else:
+            model.load_state_dict(checkpoint)
     return model.eval()
 
 

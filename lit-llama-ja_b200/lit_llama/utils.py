@@ -109,16 +109,7 @@ class EmptyInitOnDevice(torch.overrides.TorchFunctionMode):
         return func(*args, **kwargs)
 
 
-class lazy_load:
-    """ref: utils.py:364-376 - context manager yielding the checkpoint's state dict without
-    reading every tensor eagerly.  Built on ``torch.load(mmap=True)`` (pages fault in as
-    ``load_state_dict`` copies each tensor to the device) instead of a custom unpickler."""
-
-    def __init__(self, fn):
-        self.sd = torch.load(str(fn), map_location="cpu", mmap=True, weights_only=True)
-
-    def __enter__(self):
-        return self.sd
-
-    def __exit__(self, exc_type, exc_val, exc_tb):
-        self.sd = None
+# ref: utils.py:198-376 (NotYetLoadedTensor, LazyLoadingUnpickler, lazy_load): the archive is indexed and tensors are read
+# straight from their zip records on first use; checkpoint_stream.stream_load_state_dict adds the disk -> pinned -> HBM
+# pipeline with the quantized layers' one-time repack under the read
+from .checkpoint_stream import LazyLoadingUnpickler, NotYetLoadedTensor, lazy_load, stream_load_state_dict  # noqa: E402,F401
