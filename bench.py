@@ -102,14 +102,14 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------- synthetic model
-def build_model(device, name=MODEL, group=GROUP, seed=0):
+def build_model(device, name=MODEL, group=GROUP, seed=0, mode="gptq.int4"):
     """Random-init LLaMA of the named size, RTN-quantised per group on the device."""
     import torch
     from lit_llama import LLaMA
     from lit_llama.quantization import ColBlockQuantizedLinear, rtn_quantize_
     from lit_llama.utils import EmptyInitOnDevice, quantization
 
-    with EmptyInitOnDevice(device=device, dtype=torch.bfloat16), quantization("gptq.int4", groupsize=group):
+    with EmptyInitOnDevice(device=device, dtype=torch.bfloat16), quantization(mode, groupsize=group):
         model = LLaMA.from_name(name)
     gen = torch.Generator(device=device).manual_seed(seed)
     with torch.no_grad():

@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define LL_ABI_VERSION 6
+#define LL_ABI_VERSION 7
 
 #define LL_OK 0
 #define LL_ERR_ARG (-1)         /* bad shape / dtype / null pointer */
@@ -107,6 +107,18 @@ LL_API int ll_int4_prepare(const uint8_t* qw, const void* scales, const void* ze
 #define LL_STREAM_BF16 0
 #define LL_STREAM_U8 1
 LL_API int ll_int4_stream_kind(int N, int K, int group, int M);
+
+/* GPTQ 8-bit weights (`gptq.int8`: ColBlockQuantizedLinear(bits=8), ref utils.py:182-184, quantization.py:343-347; the
+ * reference serves it only through get_weight + F.linear, quantization.py:420-421).  Stream kind LL_STREAM_W8 of the same
+ * batch-1 GEMV (ll_int4_gemv with stream_kind = LL_STREAM_W8, M = 1, group % 128 == 0): a block is 16 columns x 128 k
+ * bytes laid out as the lanes' u8 mma.m16n8k32 A-fragment registers + the (scale, -zero) tail, so the main loop is loads and
+ * MMAs only; activations as the four exact base-256 digit planes.  qw: the checkpoint buffer, logical [N][K], memory [K][N].
+ * status as in ll_int4_prepare. */
+#define LL_STREAM_W8 2
+LL_API size_t ll_q8_stream_bytes(int N, int K, int group);
+LL_API int ll_q8_gemv_supported(int N, int K, int group, int nmat, int M); /* 1 / 0 */
+LL_API int ll_q8_prepare(const uint8_t* qw, const void* scales, const void* zeros, int param_dtype, uint8_t* stream_out, int N,
+                  int K, int group, int32_t* status, ll_stream stream);
 
 #define LL_EPI_STORE 0    /* y = bf16(acc (+bias)) */
 #define LL_EPI_RESIDUAL 1 /* y (residual stream, in place) = bf16(y + bf16(acc)) */

@@ -778,11 +778,18 @@ __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
 constexpr int I8_W = 8, I8_BPW = 2, I8_KB = 128;
 constexpr int I8_BLK = I8_KB * 8 + TAIL_BYTES;
 constexpr int I8_CH = I8_W * I8_BPW, I8_CHB = I8_CH * I8_BLK, I8_NCONS = I8_W * 32;
+constexpr int I8_BLK8 = I8_KB * 16 + TAIL_BYTES;  // 8-bit weights: 16 columns x 128 k bytes + tail
 constexpr uint32_t NIB_LO = 0x0F0F0F0Fu;
 
-template <int EPI, int NORM>
+// WB = 8: the same kernel for GPTQ 8-bit weights (`gptq.int8`, ref utils.py:182-184 / quantization.py:343-347, for which
+// the reference has only its de-quantise + F.linear branch).  Stream kind 2: a block is 16 columns x 128 k bytes; its words
+// ARE the u8 A-fragment registers (lane's uint4 number i = {row g, row g + 8, row g k + 16, row g + 8 k + 16} of MMA i), so
+// the main loop has no extraction arithmetic at all: 4 LDS.128 + 4 IMMA per block.  One block per warp per chunk (a chunk
+// is again 17 KB), so any number of k-blocks per row is fine.
+template <int EPI, int NORM, int WB = 4>
 __global__ void __launch_bounds__((I8_W + 9) * 32, 1) gemv_w4a8_kernel(const __grid_constant__ Params p) {
-  constexpr int W = I8_W, BPW = I8_BPW, KB = I8_KB, BLK = I8_BLK, CH = I8_CH, CHB = I8_CHB, NCONS = I8_NCONS;
+  constexpr int W = I8_W, BPW = WB == 8 ? 1 : I8_BPW, KB = I8_KB, BLK = WB == 8 ? I8_BLK8 : I8_BLK, CH = W * BPW,
+                CHB = CH * BLK, NCONS = I8_NCONS, TAIL_OFF = WB == 8 ? KB * 16 : KB * 8;
   constexpr int MAX_SLOTS_C = 12;
   constexpr int MT = TILE_N;  // floats per (tile, matrix) result at batch 1
   constexpr bool has_norm = NORM != 0;
@@ -1088,16 +1095,25 @@ __global__ void __launch_bounds__((I8_W + 9) * 32, 1) gemv_w4a8_kernel(const __g
 #pragma unroll
       for (int b = 0; b < BPW; ++b) {
         const uint32_t blk = blk0 + b * BLK;
-        const uint4 w0 = lds128(blk + lane * 16), w1 = lds128(blk + 512 + lane * 16);
         const uint32_t xk = xs_lane + (uint32_t)(gk + b) * xs_step;
         const uint4 xa = lds128(xk), xb = lds128(xk + 16);
-        sz[b] = lds64(blk + KB * 8 + g * 8);
+        sz[b] = lds64(blk + TAIL_OFF + g * 8);
         rc[b] = lds64(rec_lane + (uint32_t)(gk + b) * rec_step);
         d[b][0] = d[b][1] = d[b][2] = d[b][3] = 0;
-        mma_u8s8_16832(d[b], w0.x & NIB_LO, (w0.x >> 4) & NIB_LO, w0.y & NIB_LO, (w0.y >> 4) & NIB_LO, xa.x, xa.y);
-        mma_u8s8_16832(d[b], w0.z & NIB_LO, (w0.z >> 4) & NIB_LO, w0.w & NIB_LO, (w0.w >> 4) & NIB_LO, xa.z, xa.w);
-        mma_u8s8_16832(d[b], w1.x & NIB_LO, (w1.x >> 4) & NIB_LO, w1.y & NIB_LO, (w1.y >> 4) & NIB_LO, xb.x, xb.y);
-        mma_u8s8_16832(d[b], w1.z & NIB_LO, (w1.z >> 4) & NIB_LO, w1.w & NIB_LO, (w1.w >> 4) & NIB_LO, xb.z, xb.w);
+        if constexpr (WB == 8) {
+          const uint4 w0 = lds128(blk + lane * 16), w1 = lds128(blk + 512 + lane * 16);
+          const uint4 w2 = lds128(blk + 1024 + lane * 16), w3 = lds128(blk + 1536 + lane * 16);
+          mma_u8s8_16832(d[b], w0.x, w0.y, w0.z, w0.w, xa.x, xa.y);
+          mma_u8s8_16832(d[b], w1.x, w1.y, w1.z, w1.w, xa.z, xa.w);
+          mma_u8s8_16832(d[b], w2.x, w2.y, w2.z, w2.w, xb.x, xb.y);
+          mma_u8s8_16832(d[b], w3.x, w3.y, w3.z, w3.w, xb.z, xb.w);
+        } else {
+          const uint4 w0 = lds128(blk + lane * 16), w1 = lds128(blk + 512 + lane * 16);
+          mma_u8s8_16832(d[b], w0.x & NIB_LO, (w0.x >> 4) & NIB_LO, w0.y & NIB_LO, (w0.y >> 4) & NIB_LO, xa.x, xa.y);
+          mma_u8s8_16832(d[b], w0.z & NIB_LO, (w0.z >> 4) & NIB_LO, w0.w & NIB_LO, (w0.w >> 4) & NIB_LO, xa.z, xa.w);
+          mma_u8s8_16832(d[b], w1.x & NIB_LO, (w1.x >> 4) & NIB_LO, w1.y & NIB_LO, (w1.y >> 4) & NIB_LO, xb.x, xb.y);
+          mma_u8s8_16832(d[b], w1.z & NIB_LO, (w1.z >> 4) & NIB_LO, w1.w & NIB_LO, (w1.w >> 4) & NIB_LO, xb.z, xb.w);
+        }
       }
 #pragma unroll
       for (int b = 0; b < BPW; ++b) {
@@ -1225,6 +1241,43 @@ __global__ void int4_repack_u8_kernel(const uint8_t* __restrict__ qw, const P* _
 }
 
 // ------------------------------------------------------------------------------------ host side
+// stream kind 2 (8-bit weights, checkpoint memory [K][N] bytes): one thread per 32-bit word (and per tail entry)
+template <typename P>
+__global__ void q8_repack_kernel(const uint8_t* __restrict__ qw, const P* __restrict__ scales, const P* __restrict__ zeros,
+                                 uint8_t* __restrict__ out, int N, int K, int group, int32_t* status) {
+  constexpr int KB = I8_KB, BLK = I8_BLK8;
+  const int G = K / KB, Gq = K / group;
+  const int words = KB * 4;
+  const int per_blk = words + TILE_N;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long nblk = (long long)(N / TILE_N) * G;
+  if (idx >= nblk * per_blk) return;
+  const long long b = idx / per_blk;
+  const int r = (int)(idx - b * per_blk);
+  const int tile = (int)(b / G), gk = (int)(b - (long long)tile * G);
+  uint8_t* blk = out + (size_t)b * BLK;
+  if (r >= words) {  // tail: entry e -> column tile*16 + (e>>1) + 8*(e&1): (scale, -zero)
+    const int e = r - words;
+    const int n = tile * TILE_N + (e >> 1) + 8 * (e & 1);
+    const int gq = (gk * KB) / group;
+    const float s = dt<P>::ld(scales, (size_t)n * Gq + gq);
+    const float zn = -dt<P>::ld(zeros, (size_t)n * Gq + gq);
+    if (!(bf16r(zn) == zn) || !(bf16r(s) == s)) atomicExch(status, 1);
+    reinterpret_cast<uint32_t*>(blk + KB * 16)[e] = (uint32_t)f32_to_bf16_bits(s) | ((uint32_t)f32_to_bf16_bits(zn) << 16);
+    return;
+  }
+  // word r = (MMA i, lane, c): c & 1 = row g or g + 8, c >> 1 = first or second 4 k of the lane's 8 k of that MMA;
+  // a lane's 32 k of the block are k = 32 tig .. 32 tig + 31 (the digit planes' order, as in stream kind 1)
+  const int i = r >> 7, lane = (r & 127) >> 2, c = r & 3;
+  const int g = lane >> 2, tig = lane & 3;
+  const int n = tile * TILE_N + g + 8 * (c & 1);
+  const int kbase = gk * KB + 32 * tig + 8 * i + 4 * (c >> 1);
+  uint32_t w = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) w |= (uint32_t)qw[(size_t)(kbase + j) * N + n] << (8 * j);
+  *reinterpret_cast<uint32_t*>(blk + i * 512 + lane * 16 + c * 4) = w;
+}
+
 struct Plan {
   int KB, KSP, BLK, W, BPW;
   int G, GT, ntiles, I, P;
@@ -1350,9 +1403,11 @@ bool i8_stream_ok(int N, int K, int group) {
   return group > 0 && group % I8_KB == 0 && K > 0 && K % group == 0 && N > 0 && N % TILE_N == 0;
 }
 bool i8_shape_ok(int N, int K, int group, int M) { return M == 1 && i8_stream_ok(N, K, group) && (K / I8_KB) % I8_BPW == 0; }
+// 8-bit weights (stream kind 2): one block per warp per chunk, so any whole number of k-blocks
+bool q8_shape_ok(int N, int K, int group, int M) { return M == 1 && i8_stream_ok(N, K, group); }
 
-int make_plan_i8(int N, int K, int group, int nmat, int grid, bool has_norm, Plan* pl, int budget = SMEM_CORESIDENT) {
-  if (!i8_shape_ok(N, K, group, 1)) {
+int make_plan_i8(int N, int K, int group, int nmat, int grid, bool has_norm, Plan* pl, int budget = SMEM_CORESIDENT, int wbits = 4) {
+  if (!(wbits == 8 ? q8_shape_ok(N, K, group, 1) : i8_shape_ok(N, K, group, 1))) {
     set_error("int4 GEMV (stream kind 1) needs M = 1, N %% 16 == 0, group %% 128 == 0, K %% 256 == 0 (N=%d K=%d group=%d)", N, K, group);
     return LL_ERR_UNSUPPORTED;
   }
@@ -1362,7 +1417,7 @@ int make_plan_i8(int N, int K, int group, int nmat, int grid, bool has_norm, Pla
     return LL_ERR_CUDA;
   }
   Plan& q = *pl;
-  q.KB = I8_KB; q.KSP = 4; q.BLK = I8_BLK; q.W = I8_W; q.BPW = I8_BPW;
+  q.KB = I8_KB; q.KSP = 4; q.BLK = wbits == 8 ? I8_BLK8 : I8_BLK; q.W = I8_W; q.BPW = wbits == 8 ? 1 : I8_BPW;
   q.G = K / I8_KB; q.GT = nmat * q.G; q.ntiles = N / TILE_N;
   const long long items = (long long)q.ntiles * q.GT;
   if (items > 0x3fffffff) {
@@ -1388,8 +1443,9 @@ int make_plan_i8(int N, int K, int group, int nmat, int grid, bool has_norm, Pla
   q.off_wv = take((size_t)q.W * nmat * TILE_N * 4);
   q.off_bar = take((size_t)(2 * MAX_SLOTS + 2) * 8);
   q.off_nw = take(has_norm ? (size_t)K * 2 : 0);
-  const size_t chb = (size_t)I8_CHB;
-  const int nch_max = (ipc_max + I8_CH - 1) / I8_CH;
+  const int ch = q.W * q.BPW;
+  const size_t chb = (size_t)ch * q.BLK;
+  const int nch_max = (ipc_max + ch - 1) / ch;
   long s = ((long)budget - (long)fixed) / (long)chb;
   if (s < 3 && nch_max > s) s = ((long)SMEM_SOLO - (long)fixed) / (long)chb;
   if (s > MAX_SLOTS) s = MAX_SLOTS;
@@ -1410,7 +1466,7 @@ constexpr int SMEM_EVEN = 116 * 1024;  // two EVEN CTAs (2 x 116 + 2 KB) exceed 
 constexpr int SMEM_ODD = 108 * 1024;
 int g_parity = 0;  // of the launch being issued: 0 none, LL_GEMV_EVEN, LL_GEMV_ODD
 
-template <int EPI, int NORM>
+template <int EPI, int NORM, int WB = 4>
 int launch_i8(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
   static size_t configured = 0;
   size_t smem = pl.smem;
@@ -1422,7 +1478,7 @@ int launch_i8(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
     static int odd_threads = 0;
     if (odd_threads == 0) {
       cudaFuncAttributes fa;
-      LL_CUDA(cudaFuncGetAttributes(&fa, gemv_w4a8_kernel<EPI, NORM>));
+      LL_CUDA(cudaFuncGetAttributes(&fa, gemv_w4a8_kernel<EPI, NORM, WB>));
       const int regs = ((fa.numRegs + 7) / 8) * 8;
       int t = ((32768 / regs) / 32 + 1) * 32;
       if (t < threads + 64) t = threads + 64;
@@ -1432,11 +1488,11 @@ int launch_i8(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
     threads = odd_threads;
   }
   if (smem > configured) {
-    if (configured == 0) prefer_max_smem(gemv_w4a8_kernel<EPI, NORM>);
-    LL_CUDA(cudaFuncSetAttribute(gemv_w4a8_kernel<EPI, NORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (configured == 0) prefer_max_smem(gemv_w4a8_kernel<EPI, NORM, WB>);
+    LL_CUDA(cudaFuncSetAttribute(gemv_w4a8_kernel<EPI, NORM, WB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  LL_CUDA(launch(gemv_w4a8_kernel<EPI, NORM>, dim3(pl.P), dim3(threads), smem, st, pdl, p));
+  LL_CUDA(launch(gemv_w4a8_kernel<EPI, NORM, WB>, dim3(pl.P), dim3(threads), smem, st, pdl, p));
   return LL_OK;
 }
 
@@ -1471,10 +1527,10 @@ int launch_plan(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
 
 int launch_plan_i8(const Params& p, const Plan& pl, bool pdl, cudaStream_t st) {
   const bool norm = p.norm_w != nullptr;
-#define SPEC_I8(e, n)                          \
-  if (p.epilogue == e && norm == (n != 0)) {   \
-    ++g_spec_counts[e][n][1];                  \
-    return launch_i8<e, n>(p, pl, pdl, st);    \
+#define SPEC_I8(e, n)                                                                               \
+  if (p.epilogue == e && norm == (n != 0)) {                                                        \
+    ++g_spec_counts[e][n][1];                                                                       \
+    return pl.BLK == I8_BLK8 ? launch_i8<e, n, 8>(p, pl, pdl, st) : launch_i8<e, n>(p, pl, pdl, st); \
   }
   SPEC_I8(LL_EPI_ROPE_KV, 1); SPEC_I8(LL_EPI_RESIDUAL, 0); SPEC_I8(LL_EPI_SWIGLU, 1); SPEC_I8(LL_EPI_STORE, 1); SPEC_I8(LL_EPI_STORE, 0);
   SPEC_I8(LL_EPI_SWIGLU, 0); SPEC_I8(LL_EPI_RESIDUAL, 1); SPEC_I8(LL_EPI_ROPE_KV, 0);
@@ -1536,6 +1592,39 @@ int ll_int4_prepare(const uint8_t* qw, const void* scales, const void* zeros, in
     return LL_ERR_UNSUPPORTED;
   }
   LL_LAUNCH_OK("int4_repack_kernel");
+  return LL_OK;
+}
+
+/* GPTQ 8-bit weights (`gptq.int8`): stream kind 2 of the batch-1 GEMV */
+size_t ll_q8_stream_bytes(int N, int K, int group) {
+  return i8_stream_ok(N, K, group) ? (size_t)(N / TILE_N) * (K / I8_KB) * I8_BLK8 : 0;
+}
+
+int ll_q8_gemv_supported(int N, int K, int group, int nmat, int M) {
+  if (!(nmat == 1 || nmat == 2) || !q8_shape_ok(N, K, group, M)) return 0;
+  Plan pl;
+  return make_plan_i8(N, K, group, nmat, 0, true, &pl, SMEM_CORESIDENT, 8) == LL_OK ? 1 : 0;
+}
+
+int ll_q8_prepare(const uint8_t* qw, const void* scales, const void* zeros, int pdt, uint8_t* out, int N, int K, int group,
+                  int32_t* status, ll_stream stream) {
+  LL_CHECK_ARG(qw && scales && zeros && out && status, "null pointer");
+  if (!i8_stream_ok(N, K, group)) {
+    set_error("q8_prepare: needs group %% 128 == 0, K %% group == 0, N %% 16 == 0 (N=%d K=%d group=%d)", N, K, group);
+    return LL_ERR_UNSUPPORTED;
+  }
+  LL_CHECK_ARG(((uintptr_t)out & 15) == 0, "stream buffer must be 16-byte aligned");
+  const long long nblk = (long long)(N / TILE_N) * (K / I8_KB);
+  const long long total = nblk * (I8_KB * 4 + TILE_N);
+  const unsigned blocks = (unsigned)((total + 255) / 256);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (pdt == LL_F32) q8_repack_kernel<float><<<blocks, 256, 0, st>>>(qw, (const float*)scales, (const float*)zeros, out, N, K, group, status);
+  else if (pdt == LL_BF16) q8_repack_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(qw, (const __nv_bfloat16*)scales, (const __nv_bfloat16*)zeros, out, N, K, group, status);
+  else {
+    set_error("q8_prepare: unsupported param dtype %d", pdt);
+    return LL_ERR_UNSUPPORTED;
+  }
+  LL_LAUNCH_OK("q8_repack_kernel");
   return LL_OK;
 }
 
@@ -1601,14 +1690,15 @@ int ll_int4_gemv(const ll_gemv_args* a, ll_stream stream) {
   }
   cudaStream_t st = (cudaStream_t)stream;
   Plan pl;
-  const bool i8 = a->stream_kind == LL_STREAM_U8;
+  const bool w8 = a->stream_kind == LL_STREAM_W8;
+  const bool i8 = a->stream_kind == LL_STREAM_U8 || w8;
   LL_CHECK_ARG(a->stream_kind == LL_STREAM_BF16 || i8, "bad stream kind %d", a->stream_kind);
   if (i8) {
-    LL_CHECK_ARG(a->M == 1 && a->epilogue != LL_EPI_PUSH, "stream kind 1 serves batch 1 with the store / residual / RoPE / SwiGLU epilogues");
+    LL_CHECK_ARG(a->M == 1 && a->epilogue != LL_EPI_PUSH, "stream kinds 1 and 2 serve batch 1 with the store / residual / RoPE / SwiGLU epilogues");
     const int par = (a->flags & LL_GEMV_PDL) ? (a->flags & (LL_GEMV_EVEN | LL_GEMV_ODD)) : 0;
     g_parity = par == LL_GEMV_EVEN || par == LL_GEMV_ODD ? par : 0;
     const int budget = g_parity == LL_GEMV_EVEN ? SMEM_EVEN : g_parity == LL_GEMV_ODD ? SMEM_ODD : SMEM_CORESIDENT;
-    if (int r = make_plan_i8(a->N, a->K, a->group, nmat, a->grid, a->norm_weight != nullptr, &pl, budget)) return r;
+    if (int r = make_plan_i8(a->N, a->K, a->group, nmat, a->grid, a->norm_weight != nullptr, &pl, budget, w8 ? 8 : 4)) return r;
     if (pl.smem > (size_t)budget) g_parity = 0;  // a row too long for the co-resident budget runs alone anyway
   } else if (int r = make_plan(a->N, a->K, a->group, nmat, a->M, a->grid, a->norm_weight != nullptr, &pl)) return r;
 

@@ -66,6 +66,9 @@ EXPORTS = {
     "ll_int4_stream_bytes": ([i32, i32, i32], sz_t),
     "ll_int4_prepare": ([vp, vp, vp, i32, vp, i32, i32, i32, i32, vp, vp], C.c_int),
     "ll_int4_stream_kind": ([i32, i32, i32, i32], C.c_int),
+    "ll_q8_stream_bytes": ([i32, i32, i32], sz_t),
+    "ll_q8_gemv_supported": ([i32, i32, i32, i32, i32], C.c_int),
+    "ll_q8_prepare": ([vp, vp, vp, i32, vp, i32, i32, i32, vp, vp], C.c_int),
     "ll_int4_gemv_plan": ([i32, i32, i32, i32, i32, i32, C.POINTER(sz_t), C.POINTER(C.c_int32)], C.c_int),
     "ll_int4_gemv": ([C.POINTER(GemvArgs), vp], C.c_int),
     "ll_gemm_bf16_tc": ([vp, vp, vp, vp, i32, i32, i32, vp], C.c_int),
@@ -94,7 +97,7 @@ EXPORTS = {
 }
 _fn = {name: _proto(name, a, r) for name, (a, r) in EXPORTS.items()}
 
-ABI_VERSION = 6
+ABI_VERSION = 7
 if _fn["ll_abi_version"]() != ABI_VERSION:
     raise ImportError("libllb200.so ABI version mismatch; rebuild with lit-llama-ja_b200/build.py")
 
@@ -157,7 +160,7 @@ def gemv_supported(N: int, K: int, group: int, nmat: int, M: int) -> bool:
     return _fn["ll_int4_gemv_plan"](N, K, group, nmat, M, 0, None, None) == 0
 
 
-STREAM_BF16, STREAM_U8 = 0, 1
+STREAM_BF16, STREAM_U8, STREAM_W8 = 0, 1, 2
 
 
 def stream_kind(N: int, K: int, group: int, M: int) -> int:

@@ -65,7 +65,7 @@ class DecodeEngine:
         h0 = model.transformer.h[0]
         shapes = [(h0.attn.c_attn, 1), (_unwrap(h0.attn.c_proj)[0], 1), (h0.mlp.c_fc1, 2), (_unwrap(h0.mlp.c_proj)[0], 1),
                   (model.lm_head, 1)]
-        return all(N.gemv_supported(l.out_features, l.in_features, l.tile_cols, nmat, B) for l, nmat in shapes)
+        return all(l.gemv_ok(B, nmat) for l, nmat in shapes)
 
     def __init__(self, model, B: int, max_seq_length: int):
         cfg = model.config
@@ -100,7 +100,7 @@ class DecodeEngine:
         lins = [model.lm_head]
         for blk in model.transformer.h:
             lins += [blk.attn.c_attn, _unwrap(blk.attn.c_proj)[0], blk.mlp.c_fc1, blk.mlp.c_fc2, _unwrap(blk.mlp.c_proj)[0]]
-        all_u8 = all(lin.stream_for(B)[1] == N.STREAM_U8 for lin in lins)
+        all_u8 = all(lin.stream_for(B)[1] in (N.STREAM_U8, N.STREAM_W8) for lin in lins)   # the integer-MMA kernel (4- or 8-bit weights)
         # tensor parallel: the exchange kernel is itself a link of the programmatic chain (LLB200_TP_PDL, default on with the
         # peer exchange) - the footprints are then needed for the same placement reason
         self.tp_pdl = (self.tp and self.use_pdl and all_u8 and os.environ.get("LLB200_TP_EXCHANGE", "ll") in ("peer", "ll")

@@ -99,8 +99,20 @@ class ColBlockQuantizedLinear(torch.nn.Module):
 
     # ------------------------------------------------------------------ int4 GEMV weight stream
     def _fast_eligible(self) -> bool:
-        return (self.bits == 4 and self.scales.dtype == self.zeros.dtype
-                and N.stream_bytes(self.out_features, self.in_features, self.tile_cols) > 0)
+        if self.scales.dtype != self.zeros.dtype:
+            return False
+        if self.bits == 8:      # gptq.int8: stream kind 2 of the batch-1 GEMV
+            return N.call_ret("ll_q8_stream_bytes", self.out_features, self.in_features, self.tile_cols) > 0
+        return self.bits == 4 and N.stream_bytes(self.out_features, self.in_features, self.tile_cols) > 0
+
+    def gemv_ok(self, M: int, nmat: int = 1) -> bool:
+        """The tensor-core GEMV takes this layer at batch ``M`` (4-bit: M <= 8; 8-bit weights: batch 1)."""
+        if self.bits == 8:
+            return bool(N.call_ret("ll_q8_gemv_supported", self.out_features, self.in_features, self.tile_cols, nmat, M))
+        return self.bits == 4 and N.gemv_supported(self.out_features, self.in_features, self.tile_cols, nmat, M)
+
+    def _kind(self, M: int) -> int:
+        return N.STREAM_W8 if self.bits == 8 else N.stream_kind(self.out_features, self.in_features, self.tile_cols, M)
 
     def _state_key(self):
         return (self.quant_weight.data_ptr(), self.scales.data_ptr(), self.zeros.data_ptr(),
@@ -112,10 +124,9 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         128-multiple scale groups takes the integer-MMA kernel's layout, everything else the bf16 kernel's
         (``ll_int4_stream_kind``).  Returns the stream, or ``None`` when the layer cannot take the tensor-core GEMV
         (shape, or scales / zeros not exactly representable in bf16)."""
-        if not self._fast_eligible():
+        if not self._fast_eligible() or (self.bits == 8 and not self.gemv_ok(M)):
             return None
-        kind = N.stream_kind(self.out_features, self.in_features, self.tile_cols, M)
-        return self._prepare_kind(kind)
+        return self._prepare_kind(self._kind(M))
 
     def _prepare_kind(self, kind: int):
         ent = self._streams.get(kind)
@@ -123,12 +134,19 @@ class ColBlockQuantizedLinear(torch.nn.Module):
             return ent[1] if ent[2] else None
         qw = self._packed_ptr_ok()
         dev = self.scales.device
-        nbytes = N.stream_bytes(self.out_features, self.in_features, self.tile_cols)
-        buf = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         status = torch.zeros(1, dtype=torch.int32, device=dev)
-        N.call("ll_int4_prepare", N.ptr(qw), N.ptr(self.scales.contiguous()), N.ptr(self.zeros.contiguous()),
-               N.dtype_code(self.scales.dtype), N.ptr(buf), self.out_features, self.in_features, self.tile_cols, kind,
-               N.ptr(status), N.stream())
+        if kind == N.STREAM_W8:
+            nbytes = N.call_ret("ll_q8_stream_bytes", self.out_features, self.in_features, self.tile_cols)
+            buf = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+            N.call("ll_q8_prepare", N.ptr(qw), N.ptr(self.scales.contiguous()), N.ptr(self.zeros.contiguous()),
+                   N.dtype_code(self.scales.dtype), N.ptr(buf), self.out_features, self.in_features, self.tile_cols,
+                   N.ptr(status), N.stream())
+        else:
+            nbytes = N.stream_bytes(self.out_features, self.in_features, self.tile_cols)
+            buf = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+            N.call("ll_int4_prepare", N.ptr(qw), N.ptr(self.scales.contiguous()), N.ptr(self.zeros.contiguous()),
+                   N.dtype_code(self.scales.dtype), N.ptr(buf), self.out_features, self.in_features, self.tile_cols, kind,
+                   N.ptr(status), N.stream())
         ok = int(status.item()) == 0
         self._streams[kind] = (self._state_key(), buf, ok)
         return buf if ok else None
@@ -146,7 +164,7 @@ class ColBlockQuantizedLinear(torch.nn.Module):
 
     def stream_for(self, M: int):
         """(prepared stream, its kind) for batch ``M`` WITHOUT building it (safe under CUDA-graph capture), or (None, kind)."""
-        kind = N.stream_kind(self.out_features, self.in_features, self.tile_cols, M)
+        kind = self._kind(M)
         ent = self._streams.get(kind)
         return ((ent[1] if ent is not None and ent[2] else None), kind)
 
@@ -167,7 +185,7 @@ class ColBlockQuantizedLinear(torch.nn.Module):
         if M == 0:
             return inp.new_empty(out_shape)
         y = torch.empty((M, Nout), device=inp.device, dtype=inp.dtype)
-        fast = inp.dtype == torch.bfloat16 and M <= 8 and N.gemv_supported(Nout, K, self.tile_cols, 1, M)
+        fast = inp.dtype == torch.bfloat16 and M <= 8 and self.gemv_ok(M)
         if fast and torch.cuda.is_current_stream_capturing():
             fast = self.stream_for(M)[0] is not None   # the stream must have been prepared before capture
         elif fast:

@@ -47,14 +47,14 @@ def _lin_names(n_layer):
     return names
 
 
-def build_cfg2_model(group, n_layer=2, seed=0):
+def build_cfg2_model(group, n_layer=2, seed=0, mode="gptq.int4"):
     """Random-init model of 7B layer shapes, RTN-quantised on-grid per group, norm scales 1 +- 0.1."""
     from lit_llama import LLaMA, LLaMAConfig
     from lit_llama.quantization import ColBlockQuantizedLinear, rtn_quantize_
     from lit_llama.utils import EmptyInitOnDevice, quantization
 
     cfg = LLaMAConfig(**{**CFG2, "n_layer": n_layer})
-    with EmptyInitOnDevice(device=DEV, dtype=torch.bfloat16), quantization("gptq.int4", groupsize=group):
+    with EmptyInitOnDevice(device=DEV, dtype=torch.bfloat16), quantization(mode, groupsize=group):
         m = LLaMA(cfg)
     gen = torch.Generator(device=DEV).manual_seed(seed)
     with torch.no_grad():
@@ -69,14 +69,14 @@ def build_cfg2_model(group, n_layer=2, seed=0):
     return m.eval()
 
 
-def oracle_of(m, group):
+def oracle_of(m, group, bits=4):
     """oracle/model.py over the SAME quantized state (checkpoint-layout buffers read back from the device)."""
     cfg = m.config
     sd = m.state_dict()
     lin = {}
     for n in _lin_names(cfg.n_layer):
         lin[n] = OM.QLinear(sd[n + ".quant_weight"].cpu().numpy(), sd[n + ".scales"].float().cpu().numpy(),
-                            sd[n + ".zeros"].float().cpu().numpy(), 4, group, cache=True)
+                            sd[n + ".zeros"].float().cpu().numpy(), bits, group, cache=True)
     norms = {k: v.float().cpu().numpy() for k, v in sd.items() if k.endswith(".scale")}
     ocfg = OM.Config(block_size=cfg.block_size, vocab_size=cfg.vocab_size, n_layer=cfg.n_layer, n_head=cfg.n_head, n_embd=cfg.n_embd)
     return OM.LLaMA(ocfg, lin, sd["transformer.wte.weight"].float().cpu().numpy(), norms, "bf16")
@@ -183,6 +183,34 @@ def test_fused_decode_chain_at_7b_shapes_vs_oracle_and_module_path(g128, msl, n_
     # deterministic run to run
     again = run_ours(m, idx, msl, n_prefill, fused=True)
     assert np.array_equal(fused, again)
+
+
+def test_gptq_int8_fused_decode_chain_at_7b_shapes_vs_oracle_and_module_path():
+    """gptq.int8 (8-bit GPTQ weights, group 128) through the same fused decode chain: every Linear takes stream kind 2 of
+    the batch-1 GEMV; against the oracle with the reference's rounding rules at 8 bits and the per-module path."""
+    from lit_llama import _native as NV
+
+    m = build_cfg2_model(128, mode="gptq.int8")
+    assert m.lm_head.bits == 8
+    o = oracle_of(m, 128, bits=8)
+    msl, n_prefill, n_steps = 768, PROMPT, 24
+    idx = tokens(n_prefill + n_steps, seed=8)
+    m._engine = None
+    gemv_counts(reset=True)
+    fused = run_ours(m, idx, msl, n_prefill, fused=True)
+    eng = m._engine
+    assert eng is not None and eng.n_replays > 0, "the fused engine did not run for gptq.int8"
+    assert eng.layers[0][0].stream_kind == NV.STREAM_W8 and eng.parity
+    spec, generic = gemv_counts()
+    for e, n in ((NV.EPI_ROPE_KV, 1), (NV.EPI_RESIDUAL, 0), (NV.EPI_SWIGLU, 1), (NV.EPI_STORE, 1)):
+        assert spec[e, n, 1] > 0, spec.tolist()
+    module = run_ours(m, idx, msl, n_prefill, fused=False)
+    want = run_oracle(o, idx, msl, n_prefill)
+    rec = {}
+    check("gptq.int8 fused engine vs oracle", fused, want, rec)
+    check("gptq.int8 per-module path vs oracle", module, want, rec)
+    check("gptq.int8 fused engine vs per-module path", fused, module, rec)
+    assert np.array_equal(fused, run_ours(m, idx, msl, n_prefill, fused=True))
 
 
 @pytest.mark.parametrize("group", [128])
@@ -359,13 +387,16 @@ def test_staged_attention_behind_c_attn_as_programmatic_dependent(S, pos):
         assert np.array_equal(chain(True)[0], plain)
 
 
+BITS = 4   # weight width the helpers below build layers with (the gptq.int8 test switches it to 8)
+
+
 def _bf16_layer(N_, K, group, seed):
     from oracle import quant as OQ
 
     r = np.random.RandomState(seed)
-    Q, s, z = OQ.rtn_quantize((r.randn(N_, K) * 0.02).astype(np.float32), 4, group)
+    Q, s, z = OQ.rtn_quantize((r.randn(N_, K) * 0.02).astype(np.float32), BITS, group)
     s, z = OQ.bf16_round(s), OQ.bf16_round(z)
-    return OQ.pack_weight(Q, s, z, 4, group, "bf16"), s, z
+    return OQ.pack_weight(Q, s, z, BITS, group, "bf16"), s, z
 
 
 def _stream_of(packed, s, z, N_, K, group, M=1):
@@ -373,7 +404,7 @@ def _stream_of(packed, s, z, N_, K, group, M=1):
 
     torch.set_default_dtype(torch.bfloat16)
     try:
-        lin = ColBlockQuantizedLinear(K, N_, False, bits=4, tile_cols=group)
+        lin = ColBlockQuantizedLinear(K, N_, False, bits=BITS, tile_cols=group)
     finally:
         torch.set_default_dtype(torch.float32)
     lin = lin.to(DEV)
@@ -386,13 +417,13 @@ def _stream_of(packed, s, z, N_, K, group, M=1):
 def _exact(x, packed, s, z, group):
     from oracle import quant as OQ
 
-    return OQ.linear_forward_exact(x, packed, s, z, 4, group)
+    return OQ.linear_forward_exact(x, packed, s, z, BITS, group)
 
 
 def _mag(x, packed, s, z, group):
     from oracle import quant as OQ
 
-    return np.abs(x).astype(np.float64) @ np.abs(OQ.get_weight(packed, s, z, 4, group)).astype(np.float64).T
+    return np.abs(x).astype(np.float64) @ np.abs(OQ.get_weight(packed, s, z, BITS, group)).astype(np.float64).T
 
 
 @pytest.mark.parametrize("M", [1, 2])
@@ -507,6 +538,43 @@ def test_specialised_gemv_epilogues_with_fused_norm_at_7b_shapes(M):
     m1 = 1 if M == 1 else 0
     for e, n in ((NV.EPI_ROPE_KV, 1), (NV.EPI_RESIDUAL, 0), (NV.EPI_SWIGLU, 1), (NV.EPI_STORE, 1)):
         assert spec[e, n, m1] > 0, spec.tolist()
+
+
+def test_q8_gemv_epilogues_at_7b_shapes(monkeypatch):
+    """gptq.int8 (ColBlockQuantizedLinear bits = 8, ref utils.py:182-184): stream kind 2 of the batch-1 GEMV - the same
+    five layer kinds of the decode chain with every fused prologue / epilogue, against the exact oracle at 8 bits; then a
+    row with an ODD number of 128-element k-blocks (43), a ragged last CTA share and canary rows around the output."""
+    import sys
+    from lit_llama import _native as NV
+    from oracle import quant as OQ
+
+    monkeypatch.setattr(sys.modules[__name__], "BITS", 8)
+    test_specialised_gemv_epilogues_with_fused_norm_at_7b_shapes(1)
+    N_, K, group = 1040, 5504, 128
+    pk, s, z = _bf16_layer(N_, K, group, 33)
+    lin = _stream_of(pk, s, z, N_, K, group, 1)
+    x = OQ.bf16_round(np.random.RandomState(6).randn(1, K).astype(np.float32))
+    buf = torch.full((3, N_), 1024.0, device=DEV, dtype=torch.bfloat16)
+    a = NV.GemvArgs()
+    w, a.stream_kind = lin.stream_for(1)
+    assert a.stream_kind == NV.STREAM_W8 and w is not None
+    a.w, a.N, a.K, a.group, a.M = w.data_ptr(), N_, K, group, 1
+    xd = torch.from_numpy(x).to(DEV, torch.bfloat16)
+    a.x, a.y = xd.data_ptr(), buf[1:].data_ptr()
+    a.epilogue, a.flags, a.grid = NV.EPI_STORE, 0, 0
+    NV.gemv(a)
+    torch.cuda.synchronize()
+    got = buf.float().cpu().numpy()
+    assert (got[0] == 1024.0).all() and (got[2] == 1024.0).all()
+    exact = _exact(x, pk, s, z, group)
+    assert (np.abs(got[1:2] - exact) <= np.abs(exact) * 2.0 ** -8 + _mag(x, pk, s, z, group) * 2.0 ** -18 + 1e-30).all()
+    # the module's forward takes the same route at batch 1 and the reference-semantics kernel at batch 2
+    y1 = lin(xd).float().cpu().numpy()
+    assert np.array_equal(y1, got[1:2])
+    x2 = torch.cat([xd, xd])
+    y2 = lin(x2).float().cpu().numpy()
+    ref = OQ.linear_forward(OQ.bf16_round(np.concatenate([x, x])), pk, s, z, None, 8, group, "bf16")
+    assert np.abs(y2 - ref).max() <= 2.0 ** -6 * np.abs(ref).max()
 
 
 @pytest.mark.parametrize("M", [1, 2])
