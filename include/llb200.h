@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define LL_ABI_VERSION 7
+#define LL_ABI_VERSION 8
 
 #define LL_OK 0
 #define LL_ERR_ARG (-1)         /* bad shape / dtype / null pointer */
@@ -238,6 +238,13 @@ LL_API int ll_gptq_block(float* W, int ldw, const float* Hinv, int ldh, float* s
  * ------------------------------------------------------------------------------------- */
 LL_API int ll_sample_topk(const void* logits, int V, float temperature, int top_k, const float* u, int32_t* step, const int32_t* pos,
                    int64_t* out_tokens, int64_t* tok, ll_stream stream);
+/* The same draw followed, in the same kernel, by what ll_advance_pos and ll_embed_ssq do (the engine's sampled step: one
+ * launch instead of three before the first GEMV of the next token): pos (int32[3]) is advanced by one position after the
+ * token was written to out_tokens[pos[0] + 1] (a position >= max_pos traps, as ll_advance_pos), and the chosen token's row
+ * of wte [V][dim] bf16 is copied to x [dim] (ref model.py:110). */
+LL_API int ll_sample_advance_embed(const void* logits, int V, float temperature, int top_k, const float* u, int32_t* step,
+                            int32_t* pos, int64_t* out_tokens, int64_t* tok, int cache_len, int max_pos, const void* wte,
+                            void* x, int dim, ll_stream stream);
 
 /* ---------------------------------------------------------------------------------------
  * Tensor-parallel exchange (new: the reference is single-device, generate.py:122).  One-shot all-reduce over

@@ -192,13 +192,14 @@ class DecodeEngine:
         self.a_head = self._gemv_args(m.lm_head, self.x, self.logits, N.EPI_STORE, "head", norm=m.transformer.ln_f)
 
     # ------------------------------------------------------------------ one step
-    def _run_step(self):
+    def _run_step(self, embed: bool = True):
         cfg = self.model.config
         st = N.stream()
         wte = self.model.transformer.wte.weight
-        N.call("ll_embed_ssq", N.ptr(wte), N.ptr(self.tok), N.ptr(self.x), None, self.B, cfg.n_embd, st)
+        if embed:      # (the sampled step's draw kernel has already copied the token's row into x)
+            N.call("ll_embed_ssq", N.ptr(wte), N.ptr(self.tok), N.ptr(self.x), None, self.B, cfg.n_embd, st)
         flags = N.GEMV_PDL if (self.use_pdl and self.attn_pdl) else 0
-        n = 1
+        n = 1 if embed else 0
         for a_attn, kc, vc, a_proj, a_fc, a_down in self.layers:
             N.gemv(a_attn)
             N.call("ll_decode_attn", N.ptr(self.q), N.ptr(kc), N.ptr(vc), N.ptr(self.pos), N.ptr(self.att), N.LL_BF16,
@@ -341,11 +342,19 @@ class DecodeEngine:
         N.call("ll_sample_topk", N.ptr(self.logits), V, float(temperature), int(top_k) if top_k is not None else 0,
                N.ptr(self.u), N.ptr(self.draw), N.ptr(self.pos), N.ptr(self.out_tokens), N.ptr(self.tok), N.stream())
 
+    def _draw_advance_embed(self, temperature: float, top_k):
+        """One kernel: the draw of ``_draw``, then the position update of ``ll_advance_pos`` and the embedding copy of
+        ``ll_embed_ssq`` for the token just drawn (csrc/sampling.cu)."""
+        V = self.logits.shape[-1]
+        wte = self.model.transformer.wte.weight
+        N.call("ll_sample_advance_embed", N.ptr(self.logits), V, float(temperature), int(top_k) if top_k is not None else 0,
+               N.ptr(self.u), N.ptr(self.draw), N.ptr(self.pos), N.ptr(self.out_tokens), N.ptr(self.tok), self.S,
+               self.rope.shape[0], N.ptr(wte), N.ptr(self.x), wte.shape[1], N.stream())
+
     def _run_sampled(self, temperature, top_k):
-        self._draw(temperature, top_k)
-        N.call("ll_advance_pos", N.ptr(self.pos), self.S, self.rope.shape[0], N.stream())
-        self._run_step()
-        self.n_launches += 2
+        self._draw_advance_embed(temperature, top_k)
+        self._run_step(embed=False)
+        self.n_launches += 1
 
     def begin_sampling(self, prompt: torch.Tensor, last_logits: torch.Tensor, n_draws: int) -> bool:
         """Device-side state for ``n_draws`` draws after a prompt of n tokens whose last logits are given:
@@ -373,10 +382,9 @@ class DecodeEngine:
             return
         if self.graph is None:
             self._capture()
-        # run the two extra kernels once outside capture (their first launch loads them)
+        # run the draw kernel once outside capture (its first launch loads it)
         self.pos.zero_()
-        self._draw(temperature, top_k)
-        N.call("ll_advance_pos", N.ptr(self.pos), self.S, self.rope.shape[0], N.stream())
+        self._draw_advance_embed(temperature, top_k)
         self.pos.zero_()
         self.draw.zero_()
         torch.cuda.synchronize()

@@ -114,3 +114,38 @@ def test_generate_on_device_is_greedy_consistent_for_top1():
     c = G.generate(m, prompt, 10, temperature=0.8, top_k=5, eos_id=eos)
     first = 6 + int((a[6:] == eos).nonzero()[0])
     assert torch.equal(c, a[:first])
+
+
+@pytest.mark.parametrize("misaligned", [False, True])
+def test_sample_advance_embed_equals_the_three_kernels(misaligned):
+    """ll_sample_advance_embed = ll_sample_topk, ll_advance_pos, ll_embed_ssq in one launch: same token, same out_tokens
+    entry, same position triple (including the ring wrap) and the same residual row, over a run of draws; the 16-byte load
+    path of the logits and the scalar one (row at an odd offset) agree."""
+    from lit_llama import _native as N
+
+    V, dim, S, max_pos = 32000, 512, 7, 64
+    r = np.random.RandomState(11)
+    base = torch.from_numpy(OQ.bf16_round(r.randn(V + 8).astype(np.float32) * 3.0)).to(DEV, torch.bfloat16)
+    lg = base[1:1 + V] if misaligned else base[:V].clone()
+    wte = torch.from_numpy(OQ.bf16_round(r.randn(V, dim).astype(np.float32))).to(DEV, torch.bfloat16)
+    us = r.rand(12).astype(np.float32)
+    u = torch.tensor(us, device=DEV)
+
+    def state():
+        return dict(step=torch.zeros(1, dtype=torch.int32, device=DEV), pos=torch.tensor([3, 3, 4], dtype=torch.int32, device=DEV),
+                    out=torch.full((32,), -1, dtype=torch.int64, device=DEV), tok=torch.zeros(1, dtype=torch.int64, device=DEV),
+                    x=torch.zeros((1, dim), dtype=torch.bfloat16, device=DEV))
+
+    a, b = state(), state()
+    for _ in range(len(us)):
+        N.call("ll_sample_topk", N.ptr(lg), V, 0.8, 200, N.ptr(u), N.ptr(a["step"]), N.ptr(a["pos"]), N.ptr(a["out"]), N.ptr(a["tok"]),
+               N.stream())
+        N.call("ll_advance_pos", N.ptr(a["pos"]), S, max_pos, N.stream())
+        N.call("ll_embed_ssq", N.ptr(wte), N.ptr(a["tok"]), N.ptr(a["x"]), None, 1, dim, N.stream())
+        N.call("ll_sample_advance_embed", N.ptr(lg), V, 0.8, 200, N.ptr(u), N.ptr(b["step"]), N.ptr(b["pos"]), N.ptr(b["out"]),
+               N.ptr(b["tok"]), S, max_pos, N.ptr(wte), N.ptr(b["x"]), dim, N.stream())
+        torch.cuda.synchronize()
+        for k in a:
+            assert torch.equal(a[k], b[k]), k
+        assert torch.equal(b["x"][0], wte[int(b["tok"].item())])
+    assert b["pos"].tolist() == [15, 15 % S, S]
