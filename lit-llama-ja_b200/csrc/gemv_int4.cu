@@ -79,6 +79,7 @@ struct Params {
   int ts_max;     // (tile, matrix) slots of the cross-warp reduction
   int off_xs, off_sx, off_red, off_wv, off_bar, off_nw;
   int prefetch_delay_ns;  // producer start delay under PDL (lets the running kernel's x staging go first)
+  int helpers;            // batch-1 kernel, ODD footprint, no fused norm: the parked warps convert x too before they park
   unsigned long long* trace;  // debug: [P][8] globaltimer stamps of this launch, or nullptr
 };
 
@@ -822,9 +823,13 @@ __global__ void __launch_bounds__((I8_W + 9) * 32, 1) gemv_w4a8_kernel(const __g
   }
   __syncthreads();
   pdl_launch_dependents();
-  if (warp > W) {
-    // idle warps of an ODD-parity launch: they only widen the CTA's register footprint, so they must stay resident (an
-    // exited warp gives its registers back) - parked on a named barrier that warp 0 releases at the end
+  // idle warps of an ODD-parity launch: they only widen the CTA's register footprint, so they must stay resident (an
+  // exited warp gives its registers back) - parked on a named barrier that warp 0 releases at the end.  p.helpers (kernels
+  // without the fused norm): before parking they take their share of the x conversion, which runs at 0.45 instructions per
+  // clock with two warps per scheduler (dependent-instruction latency): more warps shorten it.
+  const bool helper = warp > W;
+  const bool helping = !has_norm && p.helpers != 0;  // uniform over the CTA
+  if (helper && !helping) {
     asm volatile("bar.sync 2, %0;" ::"r"((int)blockDim.x - W * 32) : "memory");
     return;
   }
@@ -874,6 +879,9 @@ __global__ void __launch_bounds__((I8_W + 9) * 32, 1) gemv_w4a8_kernel(const __g
 
   uint8_t* nws = smem + p.off_nw;
   uint64_t* xbar = full + 2 * MAX_SLOTS_C;
+  // threads that convert x: the 256 consumer threads, plus the helper warps (numbered after them; the producer warp is not one)
+  const int stid = helper ? NCONS + ((int)threadIdx.x - (W + 1) * 32) : ctid;
+  const int nst = helping ? (int)blockDim.x - 32 : NCONS;
   if (ctid == 0) {
     mbar_init(&xbar[1], 1);
     fence_barrier_init();
@@ -882,10 +890,15 @@ __global__ void __launch_bounds__((I8_W + 9) * 32, 1) gemv_w4a8_kernel(const __g
       bulk_load_1d(nws, p.norm_w, (uint32_t)p.K * 2, &xbar[1]);
     }
   }
-  for (int i = ctid; i < nvt * W * MT; i += NCONS) red[i] = 0.f;
-  if (ctid < 32) *reinterpret_cast<uint32_t*>(xs + 4 * (size_t)pstride + ctid * 4) = 0u;  // zero area of the B fragments
-  if (ctid < 4) rec[(size_t)G * 4 + ctid] = 0.f;                                           // and of the records
-  consumer_sync(NCONS);
+  if (!helper) {
+    for (int i = ctid; i < nvt * W * MT; i += NCONS) red[i] = 0.f;
+    if (ctid < 32) *reinterpret_cast<uint32_t*>(xs + 4 * (size_t)pstride + ctid * 4) = 0u;  // zero area of the B fragments
+    if (ctid < 4) rec[(size_t)G * 4 + ctid] = 0.f;                                           // and of the records
+  }
+  // every converting thread meets here once before the staging (also what tells ptxas that the warps are converged: without
+  // a barrier in front of it every shuffle of the staging loop is compiled behind a WARPSYNC)
+  if (helping) asm volatile("bar.sync 3, %0;" ::"r"(nst) : "memory");
+  else consumer_sync(NCONS);
 
   TRACE(1);
   pdl_wait();
@@ -910,7 +923,7 @@ __global__ void __launch_bounds__((I8_W + 9) * 32, 1) gemv_w4a8_kernel(const __g
   auto fetch = [&](int v0) {
 #pragma unroll
     for (int j = 0; j < XR; ++j) {
-      const int v = v0 + j * NCONS + ctid;
+      const int v = v0 + j * nst + stid;
       raw[j] = v < vpr ? __ldcg(xsrc + v) : make_uint4(0u, 0u, 0u, 0u);
     }
   };
@@ -955,12 +968,12 @@ __global__ void __launch_bounds__((I8_W + 9) * 32, 1) gemv_w4a8_kernel(const __g
     mbar_wait_u32(smem_u32(&xbar[1]), 0);
     TRACE(7);
   }
-  for (int v0 = 0; v0 < vpr; v0 += XR * NCONS) {
+  for (int v0 = 0; v0 < vpr; v0 += XR * nst) {
     if (v0 > 0) fetch(v0);
 #pragma unroll
     for (int j = 0; j < XR; ++j) {
-      if (v0 + j * NCONS >= vpr) continue;  // uniform over the CTA
-      const int v = v0 + j * NCONS + ctid;
+      if (v0 + j * nst >= vpr) continue;  // uniform over the CTA
+      const int v = v0 + j * nst + stid;
       const bool ok = v < vpr;  // uniform over a half-warp: K is a multiple of 128
       uint32_t wd[4] = {raw[j].x, raw[j].y, raw[j].z, raw[j].w};
       if (has_norm) {  // ref model.py:276-283 rounding steps: bf16(w * bf16(x * r))
@@ -1018,7 +1031,17 @@ __global__ void __launch_bounds__((I8_W + 9) * 32, 1) gemv_w4a8_kernel(const __g
     }
   }
   TRACE(10);
-  consumer_sync(NCONS);
+  if (helping) {
+    // the consumers wait for every converting thread on named barrier 3; the helper warps only arrive, then park
+    if (helper) {
+      asm volatile("bar.arrive 3, %0;" ::"r"(nst) : "memory");
+      asm volatile("bar.sync 2, %0;" ::"r"((int)blockDim.x - W * 32) : "memory");
+      return;
+    }
+    asm volatile("bar.sync 3, %0;" ::"r"(nst) : "memory");
+  } else {
+    consumer_sync(NCONS);
+  }
   TRACE(3);
 
   // epilogue operands that do not depend on this kernel's sums, fetched for this warp's first tile behind the main loop
@@ -1736,6 +1759,12 @@ int ll_int4_gemv(const ll_gemv_args* a, ll_stream stream) {
     delay_ns = e ? atoi(e) : 0;
   }
   p.prefetch_delay_ns = pdl ? delay_ns : 0;
+  {
+    // LLB200_GEMV_HELPERS=0: the parked warps of an ODD launch do not take part in the x conversion (A/B measurements);
+    // read per launch: the chain is captured into a graph once
+    const char* e = getenv("LLB200_GEMV_HELPERS");
+    p.helpers = (i8 && g_parity == LL_GEMV_ODD && a->norm_weight == nullptr && (e ? atoi(e) != 0 : true)) ? 1 : 0;
+  }
   return i8 ? launch_plan_i8(p, pl, pdl, st) : launch_plan(p, pl, pdl, st);
 }
 
