@@ -968,64 +968,100 @@ __global__ void __launch_bounds__((I8_W + 9) * 32, 1) gemv_w4a8_kernel(const __g
     mbar_wait_u32(smem_u32(&xbar[1]), 0);
     TRACE(7);
   }
+  // The conversion of one piece is a chain of dependent instructions (normalise, block maximum and sum over 16 lanes,
+  // exponent, digits, byte transposition): NP pieces of a thread go through it side by side - two with the fused norm
+  // (K = 4096: exactly the thread's two pieces), one otherwise (with helper warps most threads have a single piece).
+  constexpr int NP = has_norm ? 2 : 1;
   for (int v0 = 0; v0 < vpr; v0 += XR * nst) {
     if (v0 > 0) fetch(v0);
 #pragma unroll
-    for (int j = 0; j < XR; ++j) {
+    for (int j = 0; j < XR; j += NP) {
       if (v0 + j * nst >= vpr) continue;  // uniform over the CTA
-      const int v = v0 + j * nst + stid;
-      const bool ok = v < vpr;  // uniform over a half-warp: K is a multiple of 128
-      uint32_t wd[4] = {raw[j].x, raw[j].y, raw[j].z, raw[j].w};
-      if (has_norm) {  // ref model.py:276-283 rounding steps: bf16(w * bf16(x * r))
-        uint4 nraw = make_uint4(0u, 0u, 0u, 0u);
-        if (ok) nraw = *reinterpret_cast<const uint4*>(nws + (size_t)v * 16);
-        const uint32_t nw[4] = {nraw.x, nraw.y, nraw.z, nraw.w};
+      int v[NP];
+      bool ok[NP];
+      uint32_t wd[NP][4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) wd[e] = bf16x2_mul(nw[e], bf16x2_mul(wd[e], rn2));
+      for (int q = 0; q < NP; ++q) {
+        v[q] = v0 + (j + q) * nst + stid;
+        ok[q] = v[q] < vpr;  // uniform over a half-warp: K is a multiple of 128
+        wd[q][0] = raw[j + q].x; wd[q][1] = raw[j + q].y; wd[q][2] = raw[j + q].z; wd[q][3] = raw[j + q].w;
+      }
+      if (has_norm) {  // ref model.py:276-283 rounding steps: bf16(w * bf16(x * r))
+        uint4 nraw[NP];
+#pragma unroll
+        for (int q = 0; q < NP; ++q) {
+          nraw[q] = make_uint4(0u, 0u, 0u, 0u);
+          if (ok[q]) nraw[q] = *reinterpret_cast<const uint4*>(nws + (size_t)v[q] * 16);
+        }
+#pragma unroll
+        for (int q = 0; q < NP; ++q) {
+          const uint32_t nw[4] = {nraw[q].x, nraw[q].y, nraw[q].z, nraw[q].w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) wd[q][e] = bf16x2_mul(nw[e], bf16x2_mul(wd[q][e], rn2));
+        }
       }
       // the block's exponent from the largest magnitude of its 128 elements (16 lanes); the sum of the block for the zero term
-      uint32_t m2 = bf16x2_max(bf16x2_max(wd[0] & 0x7fff7fffu, wd[1] & 0x7fff7fffu), bf16x2_max(wd[2] & 0x7fff7fffu, wd[3] & 0x7fff7fffu));
-      float sum = 0.f;
+      uint32_t m2[NP];
+      float sum[NP];
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        sum = fhfma_lo(wd[e], ONE2, sum);
-        sum = fhfma_hi(wd[e], ONE2, sum);
+      for (int q = 0; q < NP; ++q) {
+        m2[q] = bf16x2_max(bf16x2_max(wd[q][0] & 0x7fff7fffu, wd[q][1] & 0x7fff7fffu),
+                           bf16x2_max(wd[q][2] & 0x7fff7fffu, wd[q][3] & 0x7fff7fffu));
+        float s0 = 0.f, s1 = 0.f;  // two chains
+#pragma unroll
+        for (int e = 0; e < 4; e += 2) {
+          s0 = fhfma_lo(wd[q][e], ONE2, s0);
+          s1 = fhfma_lo(wd[q][e + 1], ONE2, s1);
+          s0 = fhfma_hi(wd[q][e], ONE2, s0);
+          s1 = fhfma_hi(wd[q][e + 1], ONE2, s1);
+        }
+        sum[q] = s0 + s1;
       }
 #pragma unroll
       for (int o = 8; o > 0; o >>= 1) {
-        m2 = bf16x2_max(m2, __shfl_xor_sync(0xffffffffu, m2, o));
-        sum += __shfl_xor_sync(0xffffffffu, sum, o);
-      }
-      int ex = (int)max((m2 >> 7) & 0xffu, (m2 >> 23) & 0xffu);  // biased exponent of the largest magnitude: am < 2^(ex - 126)
-      ex = max(ex, 32);                                            // all-zero / denormal blocks: any finite scale will do
-      const uint32_t scale2 = ((uint32_t)(283 - ex) << 7) * 0x00010001u;  // bf16x2 2^(156 - ex): am * scale < 2^30
-      const float inv = __uint_as_float((uint32_t)(ex - 29) << 23);       // 2^-(156 - ex)
-      uint32_t u[8];
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const int v0i = __float2int_rn(fhfma_lo(wd[e], scale2, 0.f)), v1i = __float2int_rn(fhfma_hi(wd[e], scale2, 0.f));
-        u[2 * e] = ((uint32_t)v0i + 0x00808080u) ^ 0x00808080u;  // bytes = four signed base-256 digits
-        u[2 * e + 1] = ((uint32_t)v1i + 0x00808080u) ^ 0x00808080u;
-      }
-      if (ok) {
-        // 4 x 4 byte transpositions: plane d gets byte d of eight consecutive elements
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const uint32_t a = prmt(u[4 * h], u[4 * h + 1], 0x5140u), b = prmt(u[4 * h], u[4 * h + 1], 0x7362u);
-          const uint32_t cc = prmt(u[4 * h + 2], u[4 * h + 3], 0x5140u), d = prmt(u[4 * h + 2], u[4 * h + 3], 0x7362u);
-          uint8_t* dst = xs + (size_t)v * 8 + h * 4;
-          *reinterpret_cast<uint32_t*>(dst) = prmt(a, cc, 0x5410u);
-          *reinterpret_cast<uint32_t*>(dst + pstride) = prmt(a, cc, 0x7632u);
-          *reinterpret_cast<uint32_t*>(dst + 2 * (size_t)pstride) = prmt(b, d, 0x5410u);
-          *reinterpret_cast<uint32_t*>(dst + 3 * (size_t)pstride) = prmt(b, d, 0x7632u);
+        for (int q = 0; q < NP; ++q) {
+          m2[q] = bf16x2_max(m2[q], __shfl_xor_sync(0xffffffffu, m2[q], o));
+          sum[q] += __shfl_xor_sync(0xffffffffu, sum[q], o);
         }
-        if ((lane & 15) == 0) {  // record of the block: lanes tig = 0 take (inv, sum x), lanes tig = 1 take (inv * 2^16, 0)
-          float4 r;
-          r.x = inv;
-          r.y = sum;
-          r.z = inv * 65536.f;
-          r.w = 0.f;
-          *reinterpret_cast<float4*>(rec + (size_t)(v >> 4) * 4) = r;
+      }
+      uint32_t u[NP][8];
+      float inv[NP];
+#pragma unroll
+      for (int q = 0; q < NP; ++q) {
+        int ex = (int)max((m2[q] >> 7) & 0xffu, (m2[q] >> 23) & 0xffu);  // biased exponent of the largest magnitude: am < 2^(ex - 126)
+        ex = max(ex, 32);                                                  // all-zero / denormal blocks: any finite scale will do
+        const uint32_t scale2 = ((uint32_t)(283 - ex) << 7) * 0x00010001u;  // bf16x2 2^(156 - ex): am * scale < 2^30
+        inv[q] = __uint_as_float((uint32_t)(ex - 29) << 23);                // 2^-(156 - ex)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int v0i = __float2int_rn(fhfma_lo(wd[q][e], scale2, 0.f)), v1i = __float2int_rn(fhfma_hi(wd[q][e], scale2, 0.f));
+          u[q][2 * e] = ((uint32_t)v0i + 0x00808080u) ^ 0x00808080u;  // bytes = four signed base-256 digits
+          u[q][2 * e + 1] = ((uint32_t)v1i + 0x00808080u) ^ 0x00808080u;
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < NP; ++q) {
+        if (ok[q]) {
+          // 4 x 4 byte transpositions: plane d gets byte d of eight consecutive elements
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const uint32_t a = prmt(u[q][4 * h], u[q][4 * h + 1], 0x5140u), b = prmt(u[q][4 * h], u[q][4 * h + 1], 0x7362u);
+            const uint32_t cc = prmt(u[q][4 * h + 2], u[q][4 * h + 3], 0x5140u), d = prmt(u[q][4 * h + 2], u[q][4 * h + 3], 0x7362u);
+            uint8_t* dst = xs + (size_t)v[q] * 8 + h * 4;
+            *reinterpret_cast<uint32_t*>(dst) = prmt(a, cc, 0x5410u);
+            *reinterpret_cast<uint32_t*>(dst + pstride) = prmt(a, cc, 0x7632u);
+            *reinterpret_cast<uint32_t*>(dst + 2 * (size_t)pstride) = prmt(b, d, 0x5410u);
+            *reinterpret_cast<uint32_t*>(dst + 3 * (size_t)pstride) = prmt(b, d, 0x7632u);
+          }
+          if ((lane & 15) == 0) {  // record of the block: lanes tig = 0 take (inv, sum x), lanes tig = 1 take (inv * 2^16, 0)
+            float4 r;
+            r.x = inv[q];
+            r.y = sum[q];
+            r.z = inv[q] * 65536.f;
+            r.w = 0.f;
+            *reinterpret_cast<float4*>(rec + (size_t)(v[q] >> 4) * 4) = r;
+          }
         }
       }
     }
