@@ -51,6 +51,17 @@ def split_even(n: int, unit: int, rank: int, world: int) -> Tuple[int, int]:
     return a * unit, (a + base + (1 if rank < rem else 0)) * unit
 
 
+def hidden_split_unit(H: int, tile_cols: int, in_features: int) -> int:
+    """Granularity of the row-parallel split of ``mlp.c_proj`` (and of the matching column split of c_fc1 / c_fc2): whole
+    scale groups (128 for per-row scales), doubled to 256 where H allows it - an EVEN number of 128-element k-blocks per
+    shard is what the batch-1 integer-MMA GEMV takes (csrc/gemv_int4.cu i8_shape_ok); an odd count falls back to the
+    slower bf16 kernel (7B: 86 blocks -> 44 / 42 at two ranks instead of 43 / 43; 65B at four ranks: 44, 44, 42, 42)."""
+    unit = tile_cols if tile_cols != in_features else 128 if H % 128 == 0 else 2
+    if (2 * unit) % 256 == 0 and H % (2 * unit) == 0 and unit % 256 != 0:
+        unit *= 2
+    return unit
+
+
 # ----------------------------------------------------------------------------- sharding one layer
 def _new_like(lin: ColBlockQuantizedLinear, in_features: int, out_features: int) -> ColBlockQuantizedLinear:
     dt = lin.scales.dtype
@@ -126,13 +137,7 @@ def tensor_parallelize_(model, rank: int, world: int, group=None):
         attn.c_attn = shard_column(attn.c_attn, qkv_rows(E, nh, rank, world))
         attn.c_proj = RowParallelLinear(shard_row(attn.c_proj, h0 * hs, h1 * hs, keep_bias=rank == 0), group)
         attn.n_head = h1 - h0
-        unit = mlp.c_proj.tile_cols if mlp.c_proj.tile_cols != mlp.c_proj.in_features else 128 if H % 128 == 0 else 2
-        # an EVEN number of 128-element k-blocks per shard where H allows it: the batch-1 integer-MMA GEMV takes such rows
-        # (csrc/gemv_int4.cu i8_shape_ok), an odd count falls back to the slower bf16 kernel (7B: 86 blocks -> 44 / 42 at two
-        # ranks instead of 43 / 43; 65B at four ranks: 44, 44, 42, 42 instead of 43 each)
-        if (2 * unit) % 256 == 0 and H % (2 * unit) == 0 and unit % 256 != 0:
-            unit *= 2
-        a, b = split_even(H, unit, rank, world)
+        a, b = split_even(H, hidden_split_unit(H, mlp.c_proj.tile_cols, mlp.c_proj.in_features), rank, world)
         rows = torch.arange(a, b)
         mlp.c_fc1 = shard_column(mlp.c_fc1, rows)
         mlp.c_fc2 = shard_column(mlp.c_fc2, rows)

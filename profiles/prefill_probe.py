@@ -22,3 +22,20 @@ with torch.no_grad():
         e1.record(); torch.cuda.synchronize()
         ts.append(e0.elapsed_time(e1))
 print(f"prefill 512 tokens: {min(ts[2:]):.2f} ms (runs: {' '.join(f'{t:.2f}' for t in ts)})")
+
+# the same forward captured in a CUDA graph: device time without the host's launch gaps
+s = torch.cuda.Stream()
+s.wait_stream(torch.cuda.current_stream())
+with torch.no_grad(), torch.cuda.stream(s):
+    model(idx, 768, pos)
+torch.cuda.current_stream().wait_stream(s)
+torch.cuda.synchronize()
+g = torch.cuda.CUDAGraph()
+with torch.no_grad(), torch.cuda.graph(g):
+    out = model(idx, 768, pos)
+ts = []
+for i in range(5):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
+    ts.append(e0.elapsed_time(e1))
+print(f"prefill 512 tokens as one graph replay: {min(ts):.2f} ms")

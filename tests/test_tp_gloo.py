@@ -105,3 +105,23 @@ def test_shard_modules_roundtrip_cpu():
     assert np.array_equal(r.quant_weight.numpy(), qw[:, 32:96]) and np.array_equal(r.zeros.numpy(), z[:, 1:3])
     with pytest.raises(AssertionError):
         TP.shard_row(lin, 32, 192, keep_bias=True)     # not on a group boundary
+
+
+@pytest.mark.parametrize("H", [11008, 22016, 13824])
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_hidden_split_gives_even_k_block_counts(H, world):
+    """The row-parallel split of mlp.c_proj (7B / 65B / 13B hidden sizes, group 128 and per-row): contiguous, covers H, whole
+    scale groups, and every shard holds an EVEN number of 128-element k-blocks (the batch-1 integer-MMA GEMV's shape rule)."""
+    from lit_llama.tensor_parallel import hidden_split_unit, split_even
+
+    for tile_cols in (128, H):
+        unit = hidden_split_unit(H, tile_cols, H)
+        assert unit == 256 and H % unit == 0
+        edges = [split_even(H, unit, r, world) for r in range(world)]
+        assert edges[0][0] == 0 and edges[-1][1] == H
+        for (a, b), (c, _) in zip(edges, edges[1:] + [(H, H)]):
+            assert b == c and (b - a) % 256 == 0 and b > a
+        sizes = [b - a for a, b in edges]
+        assert max(sizes) - min(sizes) <= 256
+    # a hidden size that is no multiple of 256 keeps the plain group split
+    assert hidden_split_unit(11136, 128, 11136) == 128
