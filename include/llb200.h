@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define LL_ABI_VERSION 8
+#define LL_ABI_VERSION 9
 
 #define LL_OK 0
 #define LL_ERR_ARG (-1)         /* bad shape / dtype / null pointer */
@@ -214,8 +214,10 @@ LL_API int ll_int8_quantize_weight(const void* w /*[N][K]*/, int w_dtype, int8_t
  * y[M][N] = int8 matmul of the row-quantised non-outlier part + fp16 outlier-column part (+ bias), in the
  * activation dtype.  K % 128 == 0.  workspace: ll_int8_workspace_bytes(min(M, 64), N, K) bytes, 256-byte aligned. */
 LL_API size_t ll_int8_workspace_bytes(int M, int N, int K);
-LL_API int ll_int8_linear(const void* x, int act_dtype, const int8_t* cb, const float* scb, const void* bias, void* y, int M,
-                   int N, int K, float threshold, void* workspace, size_t workspace_bytes, ll_stream stream);
+/* cbt: CB transposed, int8 [K][N] (optional, NULL = none): with it an outlier column of the weights is one contiguous row
+ * read coalesced (the outlier part then costs count * N bytes instead of one 32-byte sector per (row, outlier column)). */
+LL_API int ll_int8_linear(const void* x, int act_dtype, const int8_t* cb, const int8_t* cbt, const float* scb, const void* bias,
+                   void* y, int M, int N, int K, float threshold, void* workspace, size_t workspace_bytes, ll_stream stream);
 
 /* ---------------------------------------------------------------------------------------
  * GPTQ solver, one block of <= 128 columns (ref GPTQQuantizer.quantize, quantization.py:559-590; fp32).

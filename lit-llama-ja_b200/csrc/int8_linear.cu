@@ -177,20 +177,24 @@ __global__ void __launch_bounds__(128) int8_mm_kernel(const int8_t* __restrict__
 }
 
 // ---------------------------------------------------------------- dequantise + outlier part + store
-// One thread per output column n, all rows of the pass: the outlier part  sum_i a16[m][k_i] * fp16(CB[n][k_i] * SCB[n] / 127)
-// gathers each outlier weight once per 16 rows, eight gathers in flight (the per-(m, n) thread of the first version
-// walked the outlier list with one dependent gather per step: 54 % of a batch-32 decode step) and takes the activations from shared memory.  Per (m, n) the arithmetic and its order are
-// unchanged: fp32 fma over the outlier columns in ascending order, fp16 roundings as in the oracle.
-constexpr int FIN_ROWS = 16, FIN_COLS = 64;
+// The outlier part  sum_i a16[m][k_i] * fp16(CB[n][k_i] * SCB[n] / 127)  in fp32 with the fp16 roundings of the oracle.
+constexpr int FIN_ROWS = 16, FIN_COLS = 64, FIN_SL = 4;
+// 256 threads = 64 output columns x FIN_SL slices of the outlier list: slice s takes the chunks of 64 outlier columns number
+// s, s + 4, ... (a thread per column walking the whole list alone left two warps per SM with hundreds of dependent steps:
+// 78 us per Linear in a batch-32 step whose activations have hundreds of outlier columns, 43 % of the step); the slices'
+// partial sums are added in slice order through shared memory (deterministic), then slice 0 finishes the row group.
 template <typename T>
-__global__ void __launch_bounds__(128) int8_finish_kernel(const int32_t* __restrict__ c32, const int32_t* __restrict__ sca_bits,
+__global__ void __launch_bounds__(FIN_COLS * FIN_SL) int8_finish_kernel(const int32_t* __restrict__ c32, const int32_t* __restrict__ sca_bits,
                                                           const float* __restrict__ scb, const T* __restrict__ bias,
                                                           const __half* __restrict__ a16, const int8_t* __restrict__ cb,
+                                                          const int8_t* __restrict__ cbt,
                                                           const int32_t* __restrict__ idx, const int32_t* __restrict__ count,
                                                           T* __restrict__ y, int M, int N, int K) {
-  __shared__ float a_s[FIN_COLS][FIN_ROWS];
-  __shared__ int k_s[FIN_COLS];
-  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ float a_s[FIN_SL][FIN_COLS][FIN_ROWS];
+  __shared__ int k_s[FIN_SL][FIN_COLS];
+  __shared__ float part[FIN_SL - 1][FIN_ROWS][FIN_COLS];
+  const int col = threadIdx.x & (FIN_COLS - 1), sl = threadIdx.x / FIN_COLS;
+  const int n = blockIdx.x * FIN_COLS + col;
   const bool n_ok = n < N;
   const float sb = n_ok ? scb[n] : 0.f;
   const float bv = (n_ok && bias != nullptr) ? to_half_f32<T>(bias[n]) : 0.f;
@@ -200,42 +204,56 @@ __global__ void __launch_bounds__(128) int8_finish_kernel(const int32_t* __restr
   float acc[FIN_ROWS];
 #pragma unroll
   for (int r = 0; r < FIN_ROWS; ++r) acc[r] = 0.f;
-  for (int i0 = 0; i0 < cnt; i0 += FIN_COLS) {
-    const int ni = min(FIN_COLS, cnt - i0);
+  for (int base = 0; base < cnt; base += FIN_COLS * FIN_SL) {   // uniform over the CTA
+    const int i0 = base + sl * FIN_COLS;
+    const int ni = max(0, min(FIN_COLS, cnt - i0));
     __syncthreads();
-    if (threadIdx.x < ni) k_s[threadIdx.x] = idx[i0 + threadIdx.x];
+    if (col < ni) k_s[sl][col] = idx[i0 + col];
     __syncthreads();
-    for (int e = threadIdx.x; e < FIN_COLS * FIN_ROWS; e += blockDim.x) {
+    for (int e = col; e < FIN_COLS * FIN_ROWS; e += FIN_COLS) {   // the slice's 64 threads stage its chunk of activations
       const int i = e / FIN_ROWS, r = e - i * FIN_ROWS;
-      a_s[i][r] = (i < ni && m0 + r < M) ? __half2float(a16[(size_t)(m0 + r) * K + k_s[i]]) : 0.f;
+      a_s[sl][i][r] = (i < ni && m0 + r < M) ? __half2float(a16[(size_t)(m0 + r) * K + k_s[sl][i]]) : 0.f;
     }
     __syncthreads();
-    // eight gathers in flight per thread (the loop was bound by the latency of one dependent gather per outlier);
-    // entries past ni multiply activations that were staged as zero
+    // eight weights in flight per thread; entries past ni multiply activations that were staged as zero
     for (int i = 0; i < ni; i += 8) {
       int8_t q[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) q[j] = (i + j < ni) ? wrow[k_s[i + j]] : (int8_t)0;
+      for (int j = 0; j < 8; ++j) {
+        // cbt = CB transposed ([K][N]): an outlier column is a contiguous row of it, read coalesced over the 64 columns;
+        // without it every thread gathers single bytes out of its own weight row (one 32-byte sector each)
+        if (cbt != nullptr) q[j] = (i + j < ni && n_ok) ? cbt[(size_t)k_s[sl][i + j] * N + n] : (int8_t)0;
+        else q[j] = (i + j < ni) ? wrow[k_s[sl][i + j]] : (int8_t)0;
+      }
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float wv = __half2float(__float2half_rn(__fdiv_rn(__fmul_rn((float)q[j], sb), 127.f)));
         if (i + j < ni) {
 #pragma unroll
-          for (int r = 0; r < FIN_ROWS; ++r) acc[r] = fmaf(a_s[i + j][r], wv, acc[r]);
+          for (int r = 0; r < FIN_ROWS; ++r) acc[r] = fmaf(a_s[sl][i + j][r], wv, acc[r]);
         }
       }
     }
   }
-  if (n_ok) {
+  __syncthreads();
+  if (sl > 0) {
+#pragma unroll
+    for (int r = 0; r < FIN_ROWS; ++r) part[sl - 1][r][col] = acc[r];
+  }
+  __syncthreads();
+  if (sl == 0 && n_ok) {
 #pragma unroll
     for (int r = 0; r < FIN_ROWS; ++r) {
       const int m = m0 + r;
       if (m < M) {
+        float o = acc[r];
+#pragma unroll
+        for (int t = 0; t < FIN_SL - 1; ++t) o += part[t][r][col];   // slice order
         const float sca = __int_as_float(sca_bits[m]);
         float out = __fmul_rn(__fmul_rn(__fmul_rn((float)c32[(size_t)m * N + n], sca), sb), 1.0f / (127.0f * 127.0f));
         if (bias != nullptr) out = __fadd_rn(out, bv);
         out = __half2float(__float2half_rn(out));
-        if (cnt > 0) out = __half2float(__float2half_rn(__fadd_rn(out, __half2float(__float2half_rn(acc[r])))));
+        if (cnt > 0) out = __half2float(__float2half_rn(__fadd_rn(out, __half2float(__float2half_rn(o)))));
         dt<T>::st(y, (size_t)m * N + n, out);
       }
     }
@@ -270,8 +288,8 @@ Ws carve(void* base, int M, int N, int K) {
 using namespace llb;
 
 template <typename T>
-static int int8_linear_t(const T* x, const int8_t* cb, const float* scb, const T* bias, T* y, int M, int N, int K, float thr,
-                         void* ws_base, cudaStream_t st) {
+static int int8_linear_t(const T* x, const int8_t* cb, const int8_t* cbt, const float* scb, const T* bias, T* y, int M, int N, int K,
+                         float thr, void* ws_base, cudaStream_t st) {
   const int sms = sm_count();
   for (int m0 = 0; m0 < M; m0 += 64) {  // decode-shaped passes of up to 64 rows (weights re-read per pass)
     const int Mp = min(64, M - m0);
@@ -292,7 +310,7 @@ static int int8_linear_t(const T* x, const int8_t* cb, const float* scb, const T
 #define MM(G) int8_mm_kernel<G><<<grid, 128, 0, st>>>(cb, w.ca, w.c32, Mp, N, K, per)
     if (mg <= 1) MM(1); else if (mg <= 2) MM(2); else if (mg <= 4) MM(4); else MM(8);
 #undef MM
-    int8_finish_kernel<T><<<dim3((N + 63) / 64, (Mp + FIN_ROWS - 1) / FIN_ROWS), 64, 0, st>>>(w.c32, w.sca_bits, scb, bias, w.a16, cb, w.idx, w.count,
+    int8_finish_kernel<T><<<dim3((N + FIN_COLS - 1) / FIN_COLS, (Mp + FIN_ROWS - 1) / FIN_ROWS), FIN_COLS * FIN_SL, 0, st>>>(w.c32, w.sca_bits, scb, bias, w.a16, cb, cbt, w.idx, w.count,
                                                                     y + (size_t)m0 * N, Mp, N, K);
     LL_LAUNCH_OK("int8 linear kernels");
   }
@@ -317,19 +335,19 @@ int ll_int8_quantize_weight(const void* w, int w_dtype, int8_t* cb, float* scb, 
   return LL_OK;
 }
 
-int ll_int8_linear(const void* x, int act_dtype, const int8_t* cb, const float* scb, const void* bias, void* y, int M, int N,
-                   int K, float threshold, void* workspace, size_t workspace_bytes, ll_stream stream) {
+int ll_int8_linear(const void* x, int act_dtype, const int8_t* cb, const int8_t* cbt, const float* scb, const void* bias, void* y,
+                   int M, int N, int K, float threshold, void* workspace, size_t workspace_bytes, ll_stream stream) {
   LL_CHECK_ARG(x && cb && scb && y && workspace, "null pointer");
   LL_CHECK_ARG(M > 0 && N > 0 && K > 0 && K % 128 == 0, "int8 linear needs K %% 128 == 0 (M=%d N=%d K=%d)", M, N, K);
   LL_CHECK_ARG(((uintptr_t)cb & 15) == 0 && ((uintptr_t)workspace & 255) == 0, "cb must be 16-byte, workspace 256-byte aligned");
   LL_CHECK_ARG(workspace_bytes >= ll_int8_workspace_bytes(M < 64 ? M : 64, N, K), "workspace too small");
   cudaStream_t st = (cudaStream_t)stream;
   if (act_dtype == LL_BF16)
-    return int8_linear_t<__nv_bfloat16>((const __nv_bfloat16*)x, cb, scb, (const __nv_bfloat16*)bias, (__nv_bfloat16*)y, M, N, K, threshold, workspace, st);
+    return int8_linear_t<__nv_bfloat16>((const __nv_bfloat16*)x, cb, cbt, scb, (const __nv_bfloat16*)bias, (__nv_bfloat16*)y, M, N, K, threshold, workspace, st);
   if (act_dtype == LL_F16)
-    return int8_linear_t<__half>((const __half*)x, cb, scb, (const __half*)bias, (__half*)y, M, N, K, threshold, workspace, st);
+    return int8_linear_t<__half>((const __half*)x, cb, cbt, scb, (const __half*)bias, (__half*)y, M, N, K, threshold, workspace, st);
   if (act_dtype == LL_F32)
-    return int8_linear_t<float>((const float*)x, cb, scb, (const float*)bias, (float*)y, M, N, K, threshold, workspace, st);
+    return int8_linear_t<float>((const float*)x, cb, cbt, scb, (const float*)bias, (float*)y, M, N, K, threshold, workspace, st);
   set_error("int8_linear: unsupported activation dtype %d", act_dtype);
   return LL_ERR_UNSUPPORTED;
 }

@@ -77,7 +77,7 @@ EXPORTS = {
     "ll_int4_gemm_tc_static": ([vp, vp, vp, vp, i32, i32, i32, i32, vp], C.c_int),
     "ll_int8_quantize_weight": ([vp, i32, vp, vp, i32, i32, vp], C.c_int),
     "ll_int8_workspace_bytes": ([i32, i32, i32], sz_t),
-    "ll_int8_linear": ([vp, i32, vp, vp, vp, vp, i32, i32, i32, C.c_float, vp, sz_t, vp], C.c_int),
+    "ll_int8_linear": ([vp, i32, vp, vp, vp, vp, vp, i32, i32, i32, C.c_float, vp, sz_t, vp], C.c_int),
     "ll_gptq_block": ([vp, i32, vp, i32, vp, vp, i32, vp, i32, vp, vp, i32, i32, i32, i32, i32, vp], C.c_int),
     "ll_sample_topk": ([vp, i32, C.c_float, i32, vp, vp, vp, vp, vp, vp], C.c_int),
     "ll_sample_advance_embed": ([vp, i32, C.c_float, i32, vp, vp, vp, vp, vp, i32, i32, vp, vp, i32, vp], C.c_int),
@@ -98,7 +98,7 @@ EXPORTS = {
 }
 _fn = {name: _proto(name, a, r) for name, (a, r) in EXPORTS.items()}
 
-ABI_VERSION = 8
+ABI_VERSION = 9
 if _fn["ll_abi_version"]() != ABI_VERSION:
     raise ImportError("libllb200.so ABI version mismatch; rebuild with lit-llama-ja_b200/build.py")
 

@@ -291,6 +291,7 @@ class Linear8bitLt(torch.nn.Module):
         self.weight.SCB = torch.zeros(out_features, dtype=torch.float32, device=dev)
         self.bias = torch.nn.Parameter(torch.zeros(out_features, device=dev, dtype=dtype), requires_grad=False) if bias else None
         self._ws = None
+        self._cbt = None
 
     def _load_from_state_dict(self, state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys, error_msgs):
         key = prefix + "weight"
@@ -322,6 +323,9 @@ class Linear8bitLt(torch.nn.Module):
         N.call("ll_int8_quantize_weight", N.ptr(w), N.dtype_code(w.dtype), N.ptr(cb), N.ptr(scb), w.shape[0], w.shape[1], N.stream())
         self.weight.data = cb
         self.weight.CB, self.weight.SCB = cb, scb
+        # CB transposed ([K][N]): the outlier columns of a step are then contiguous rows (csrc/int8_linear.cu, finish kernel);
+        # a second copy of the int8 weights, built once at load time (LLB200_INT8_TRANSPOSED=0: without it)
+        self._cbt = cb.t().contiguous() if __import__("os").environ.get("LLB200_INT8_TRANSPOSED", "1") != "0" else None
 
     def forward(self, inp):
         N.require_cuda(inp, self.weight)
@@ -335,7 +339,10 @@ class Linear8bitLt(torch.nn.Module):
         need = N._fn["ll_int8_workspace_bytes"](min(M, 64), Nout, K)
         ws = _int8_workspace(x.device, need)
         bias = None if self.bias is None else self.bias.to(x.dtype)
-        N.call("ll_int8_linear", N.ptr(x), N.dtype_code(x.dtype), N.ptr(self.weight.CB), N.ptr(self.weight.SCB), N.ptr(bias),
+        cbt = getattr(self, "_cbt", None)
+        if cbt is not None and (cbt.device != x.device or cbt.shape != (K, Nout)):
+            cbt = None
+        N.call("ll_int8_linear", N.ptr(x), N.dtype_code(x.dtype), N.ptr(self.weight.CB), N.ptr(cbt), N.ptr(self.weight.SCB), N.ptr(bias),
                N.ptr(y), M, Nout, K, float(self.threshold), N.ptr(ws), ws.numel(), N.stream())
         return y.reshape(inp.shape[:-1] + (Nout,))
 
