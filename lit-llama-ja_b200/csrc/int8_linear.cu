@@ -114,6 +114,96 @@ __global__ void int8_act_quant_kernel(const __half* __restrict__ a16, const int3
   ca[(size_t)m * K + k] = (int8_t)q;
 }
 
+// ---------------------------------------------------------------- activation statistics + outlier list + quantisation, one kernel
+// What int8_act_stats_kernel, int8_compact_cols_kernel and int8_act_quant_kernel do in three launches (+ the clearing of the
+// int32 accumulator) as ONE: a CTA owns 64 feature columns for all rows of the pass.
+//   phase 1: a16 = x.half(); per column "any |a16| >= thr"; per row the absmax of the entries below thr (atomicMax);
+//            this CTA's number of outlier columns -> cta_count[]; its share of c32 cleared;
+//   grid barrier (arrival counter in the workspace; the grid is K / 64 CTAs, all resident);
+//   phase 2: CA from the final row maxima; the CTA's outlier columns appended in ascending order at the prefix sum of the
+//            counts of the CTAs before it (so the list is ascending overall, as the single-block compaction produced it).
+constexpr int PREP_T = 256, PREP_C = 64, PREP_RG = PREP_T / PREP_C;  // a CTA: 64 columns x 4 interleaved row groups
+template <typename T>
+__global__ void __launch_bounds__(PREP_T) int8_act_prep_kernel(const T* __restrict__ x, __half* __restrict__ a16, int8_t* __restrict__ ca,
+                                                              int32_t* __restrict__ sca_bits, int32_t* __restrict__ idx,
+                                                              int32_t* __restrict__ count, int32_t* __restrict__ cta_count,
+                                                              int32_t* __restrict__ arrive, int32_t* __restrict__ c32, size_t c32_words,
+                                                              int M, int K, float thr) {
+  __shared__ int s_row[64];      // per-row maxima of this CTA (float bits, >= 0), later the final row scales
+  __shared__ int s_flag[PREP_C];
+  __shared__ int s_cnt[2];
+  __shared__ int s_red[PREP_T / 32];
+  __shared__ int s_base;
+  const int tx = threadIdx.x & (PREP_C - 1), ty = threadIdx.x / PREP_C;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int k = blockIdx.x * PREP_C + tx;
+  const bool k_ok = k < K;
+  if (threadIdx.x < 64) s_row[threadIdx.x] = 0;
+  if (threadIdx.x < PREP_C) s_flag[threadIdx.x] = 0;
+  // this CTA's share of the accumulator the matmul adds into
+  for (size_t i = (size_t)blockIdx.x * PREP_T + threadIdx.x; i < c32_words; i += (size_t)gridDim.x * PREP_T) c32[i] = 0;
+  __syncthreads();
+  bool flag = false;
+  for (int m = ty; m < M; m += PREP_RG) {
+    float v = 0.f;
+    if (k_ok) {
+      const __half h = __float2half_rn(to_half_f32<T>(x[(size_t)m * K + k]));
+      a16[(size_t)m * K + k] = h;
+      v = fabsf(__half2float(h));
+    }
+    const bool big = v >= thr;
+    flag |= big;
+    float mx = big ? 0.f : v;
+    mx = warp_max(mx);
+    if (lane == 0 && mx > 0.f) atomicMax(&s_row[m], __float_as_int(mx));
+  }
+  if (flag && k_ok) s_flag[tx] = 1;   // (several row groups may store the same 1)
+  __syncthreads();
+  if (threadIdx.x < M && s_row[threadIdx.x] > 0) atomicMax(&sca_bits[threadIdx.x], s_row[threadIdx.x]);
+  const bool col_out = s_flag[tx] != 0;
+  unsigned bal = 0;
+  if (ty == 0) {   // the first 64 threads count the CTA's outlier columns
+    bal = __ballot_sync(0xffffffffu, col_out);
+    if (lane == 0) s_cnt[warp] = __popc(bal);
+  }
+  __syncthreads();
+  const int mine = s_cnt[0] + s_cnt[1];
+  if (threadIdx.x == 0) {
+    cta_count[blockIdx.x] = mine;
+    __threadfence();
+    atomicAdd(arrive, 1);
+    while (*reinterpret_cast<volatile int32_t*>(arrive) < (int32_t)gridDim.x) {
+    }
+    __threadfence();
+  }
+  __syncthreads();
+  // ---- every CTA's statistics are in: prefix of the counts before this CTA, final row scales
+  int part = 0;
+  for (int c = threadIdx.x; c < (int)blockIdx.x; c += PREP_T) part += __ldcg(cta_count + c);
+  part = __reduce_add_sync(0xffffffffu, part);
+  if (lane == 0) s_red[warp] = part;
+  if (threadIdx.x < M) s_row[threadIdx.x] = __ldcg(sca_bits + threadIdx.x);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int base = 0;
+    for (int w = 0; w < PREP_T / 32; ++w) base += s_red[w];
+    s_base = base;
+    if (blockIdx.x == gridDim.x - 1) *count = base + mine;
+  }
+  __syncthreads();
+  if (ty == 0 && col_out && k_ok) idx[s_base + (warp == 1 ? s_cnt[0] : 0) + __popc(bal & ((1u << lane) - 1u))] = k;
+  if (k_ok) {
+    for (int m = ty; m < M; m += PREP_RG) {
+      const float sca = __int_as_float(s_row[m]);
+      const float inv = __fdiv_rn(127.f, sca == 0.f ? 1.f : sca);
+      const float a = __half2float(a16[(size_t)m * K + k]);
+      float q = 0.f;
+      if (!col_out && fabsf(a) < thr) q = fminf(fmaxf(rintf(__fmul_rn(a, inv)), -127.f), 127.f);
+      ca[(size_t)m * K + k] = (int8_t)q;
+    }
+  }
+}
+
 // ---------------------------------------------------------------- int8 tensor-core matmul, split-K
 __device__ __forceinline__ void mma_s8_16832(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
                                              uint32_t b1) {
@@ -262,6 +352,7 @@ __global__ void __launch_bounds__(FIN_COLS * FIN_SL) int8_finish_kernel(const in
 
 struct Ws {
   __half* a16; int8_t* ca; int32_t* c32; int32_t* colflag; int32_t* idx; int32_t* sca_bits; int32_t* count;
+  int32_t* cta_count; int32_t* arrive;
   size_t zero_off, zero_bytes, total;
 };
 Ws carve(void* base, int M, int N, int K) {
@@ -272,11 +363,13 @@ Ws carve(void* base, int M, int N, int K) {
   w.a16 = (__half*)(p + take((size_t)M * K * 2));
   w.ca = (int8_t*)(p + take((size_t)M * K));
   w.idx = (int32_t*)(p + take((size_t)K * 4));
-  w.zero_off = o;  // everything below is cleared at the start of every call
-  w.c32 = (int32_t*)(p + take((size_t)M * N * 4));
-  w.colflag = (int32_t*)(p + take((size_t)K * 4));
+  w.c32 = (int32_t*)(p + take((size_t)M * N * 4));       // cleared by the prep kernel
+  w.colflag = (int32_t*)(p + take((size_t)K * 4));       // (unused since the fused prep kernel; kept for the layout)
+  w.cta_count = (int32_t*)(p + take((size_t)((K + PREP_C - 1) / PREP_C) * 4));
+  w.zero_off = o;  // the few words below are cleared at the start of every call (one small memset)
   w.sca_bits = (int32_t*)(p + take((size_t)M * 4));
   w.count = (int32_t*)(p + take(4));
+  w.arrive = (int32_t*)(p + take(4));
   w.zero_bytes = o - w.zero_off;
   w.total = o;
   return w;
@@ -296,9 +389,16 @@ static int int8_linear_t(const T* x, const int8_t* cb, const int8_t* cbt, const 
     Ws w = carve(ws_base, Mp, N, K);
     LL_CUDA(cudaMemsetAsync((uint8_t*)ws_base + w.zero_off, 0, w.zero_bytes, st));
     const T* xp = x + (size_t)m0 * K;
-    int8_act_stats_kernel<T><<<dim3((K + 255) / 256, (Mp + 7) / 8), 256, 0, st>>>(xp, w.a16, w.colflag, w.sca_bits, Mp, K, thr);
-    int8_compact_cols_kernel<<<1, 1024, 0, st>>>(w.colflag, w.idx, w.count, K);
-    int8_act_quant_kernel<<<dim3((K + 255) / 256, Mp), 256, 0, st>>>(w.a16, w.colflag, w.sca_bits, w.ca, Mp, K, thr);
+    const int prep_ctas = (K + PREP_C - 1) / PREP_C;
+    if (prep_ctas <= 4 * sms) {   // the fused kernel's grid barrier needs every CTA resident (256 threads, 1.5 KB: >= 4 per SM)
+      int8_act_prep_kernel<T><<<prep_ctas, PREP_T, 0, st>>>(xp, w.a16, w.ca, w.sca_bits, w.idx, w.count, w.cta_count, w.arrive, w.c32,
+                                                          (size_t)Mp * N, Mp, K, thr);
+    } else {
+      LL_CUDA(cudaMemsetAsync(w.c32, 0, (size_t)((uint8_t*)w.cta_count - (uint8_t*)w.c32), st));   // c32 and colflag (adjacent)
+      int8_act_stats_kernel<T><<<dim3((K + 255) / 256, (Mp + 7) / 8), 256, 0, st>>>(xp, w.a16, w.colflag, w.sca_bits, Mp, K, thr);
+      int8_compact_cols_kernel<<<1, 1024, 0, st>>>(w.colflag, w.idx, w.count, K);
+      int8_act_quant_kernel<<<dim3((K + 255) / 256, Mp), 256, 0, st>>>(w.a16, w.colflag, w.sca_bits, w.ca, Mp, K, thr);
+    }
     const int ntiles = (N + 15) / 16, nkb = K / 128;
     int ksplit = (2 * sms + ntiles - 1) / ntiles;
     if (ksplit > nkb) ksplit = nkb;

@@ -34,7 +34,7 @@ def test_int8_weight_quantization_bit_exact(N, K):
 
 
 @pytest.mark.parametrize("M,N,K,outliers", [(1, 256, 512, 0), (4, 512, 1024, 3), (32, 4096, 4096, 5), (32, 1024, 11008, 11),
-                                            (7, 384, 256, 256), (100, 320, 640, 2)])
+                                            (7, 384, 256, 256), (100, 320, 640, 2), (32, 1024, 4096, 700)])
 @pytest.mark.parametrize("dt", ["bf16", "fp16"])
 def test_int8_linear_vs_oracle(M, N, K, outliers, dt):
     """int8 part is exact (int32); the fp16 scaling / outlier part differs only by fp32 summation order and
