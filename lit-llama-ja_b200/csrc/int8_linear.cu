@@ -213,13 +213,18 @@ __device__ __forceinline__ void mma_s8_16832(int (&c)[4], uint32_t a0, uint32_t 
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
-// grid (N/16 tiles, ksplit); block = 4 warps, each takes every 4th 128-k block of the CTA's k range.
+// grid (N/64, ksplit); block = 4 warps = four 16-column tiles walking the SAME 128-k blocks of the CTA's k range: the
+// quantised activations of a k-block ([rows][128] bytes) are staged once per CTA in shared memory (double-buffered, one
+// barrier per k-block) instead of being fetched from L2 by every 16-column tile (that was 2 x the weight bytes in L2
+// traffic); the next k-block's weights are requested before this one's MMAs.
 // c32[m][n] += sum_k CA[m][k] * CB[n][k]   (M <= 8 * MG rows; weights are the MMA A operand)
 template <int MG>
 __global__ void __launch_bounds__(128) int8_mm_kernel(const int8_t* __restrict__ cb, const int8_t* __restrict__ ca,
                                                       int32_t* __restrict__ c32, int M, int N, int K, int kblocks_per_split) {
+  constexpr int ROWS = MG * 8, STR = 144;  // 128 bytes of a row + 16: neighbouring rows start four banks apart
+  __shared__ __align__(16) uint8_t a_s[2][ROWS][STR];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tig = lane & 3;
-  const int n0 = blockIdx.x * 16;
+  const int n0 = (blockIdx.x * 4 + warp) * 16;
   const int nkb = K / 128;
   const int kb0 = blockIdx.y * kblocks_per_split, kb1 = min(kb0 + kblocks_per_split, nkb);
   int acc[MG][4];
@@ -228,28 +233,51 @@ __global__ void __launch_bounds__(128) int8_mm_kernel(const int8_t* __restrict__
   const int8_t* w_lo = cb + (size_t)(n0 + g) * K + 16 * tig;
   const int8_t* w_hi = cb + (size_t)(n0 + g + 8) * K + 16 * tig;
   const bool n_lo_ok = n0 + g < N, n_hi_ok = n0 + g + 8 < N;
-  for (int kb = kb0 + warp; kb < kb1; kb += 4) {
+  const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+  auto stage = [&](int kb, int buf) {
+#pragma unroll
+    for (int e = threadIdx.x; e < ROWS * 8; e += 128) {
+      const int row = e >> 3, seg = e & 7;
+      uint4 v = z4;
+      if (row < M) v = __ldg(reinterpret_cast<const uint4*>(ca + (size_t)row * K + (size_t)kb * 128 + seg * 16));
+      *reinterpret_cast<uint4*>(&a_s[buf][row][seg * 16]) = v;
+    }
+  };
+  auto load_w = [&](int kb, uint4 (&w)[4]) {
     const int k = kb * 128;
-    // lane (g, tig) holds k = k + 16 tig + [0,16) (slots 0..15 of four MMAs) and k + 64 + 16 tig + [0,16)
-    const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
-    const uint4 a_lo0 = n_lo_ok ? __ldcs(reinterpret_cast<const uint4*>(w_lo + k)) : z4;
-    const uint4 a_hi0 = n_hi_ok ? __ldcs(reinterpret_cast<const uint4*>(w_hi + k)) : z4;
-    const uint4 a_lo1 = n_lo_ok ? __ldcs(reinterpret_cast<const uint4*>(w_lo + k + 64)) : z4;
-    const uint4 a_hi1 = n_hi_ok ? __ldcs(reinterpret_cast<const uint4*>(w_hi + k + 64)) : z4;
-    const uint32_t al0[4] = {a_lo0.x, a_lo0.y, a_lo0.z, a_lo0.w}, ah0[4] = {a_hi0.x, a_hi0.y, a_hi0.z, a_hi0.w};
-    const uint32_t al1[4] = {a_lo1.x, a_lo1.y, a_lo1.z, a_lo1.w}, ah1[4] = {a_hi1.x, a_hi1.y, a_hi1.z, a_hi1.w};
+    // lane (g, tig) holds k + 16 tig + [0,16) (slots 0..15 of four MMAs) and k + 64 + 16 tig + [0,16)
+    w[0] = n_lo_ok ? __ldcs(reinterpret_cast<const uint4*>(w_lo + k)) : z4;
+    w[1] = n_hi_ok ? __ldcs(reinterpret_cast<const uint4*>(w_hi + k)) : z4;
+    w[2] = n_lo_ok ? __ldcs(reinterpret_cast<const uint4*>(w_lo + k + 64)) : z4;
+    w[3] = n_hi_ok ? __ldcs(reinterpret_cast<const uint4*>(w_hi + k + 64)) : z4;
+  };
+  uint4 wcur[4], wnext[4];
+  if (kb0 < kb1) {
+    load_w(kb0, wcur);
+    stage(kb0, 0);
+  }
+  __syncthreads();
+  int buf = 0;
+  for (int kb = kb0; kb < kb1; ++kb) {
+    if (kb + 1 < kb1) {
+      load_w(kb + 1, wnext);
+      stage(kb + 1, buf ^ 1);
+    }
+    const uint32_t al0[4] = {wcur[0].x, wcur[0].y, wcur[0].z, wcur[0].w}, ah0[4] = {wcur[1].x, wcur[1].y, wcur[1].z, wcur[1].w};
+    const uint32_t al1[4] = {wcur[2].x, wcur[2].y, wcur[2].z, wcur[2].w}, ah1[4] = {wcur[3].x, wcur[3].y, wcur[3].z, wcur[3].w};
 #pragma unroll
     for (int mg = 0; mg < MG; ++mg) {
       const int m = mg * 8 + g;
-      uint4 b0 = z4, b1 = z4;
-      if (m < M) {
-        b0 = __ldg(reinterpret_cast<const uint4*>(ca + (size_t)m * K + k + 16 * tig));
-        b1 = __ldg(reinterpret_cast<const uint4*>(ca + (size_t)m * K + k + 64 + 16 * tig));
-      }
+      const uint4 b0 = *reinterpret_cast<const uint4*>(&a_s[buf][m][16 * tig]);
+      const uint4 b1 = *reinterpret_cast<const uint4*>(&a_s[buf][m][64 + 16 * tig]);
       const uint32_t bb0[4] = {b0.x, b0.y, b0.z, b0.w}, bb1[4] = {b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
       for (int j = 0; j < 4; ++j) mma_s8_16832(acc[mg], al0[j], ah0[j], al1[j], ah1[j], bb0[j], bb1[j]);
     }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) wcur[j] = wnext[j];
+    __syncthreads();
+    buf ^= 1;
   }
   // D: c0,c1 -> (n = n0+g, m = 2tig, 2tig+1); c2,c3 -> (n = n0+g+8, ...)
 #pragma unroll
@@ -399,8 +427,8 @@ static int int8_linear_t(const T* x, const int8_t* cb, const int8_t* cbt, const 
       int8_compact_cols_kernel<<<1, 1024, 0, st>>>(w.colflag, w.idx, w.count, K);
       int8_act_quant_kernel<<<dim3((K + 255) / 256, Mp), 256, 0, st>>>(w.a16, w.colflag, w.sca_bits, w.ca, Mp, K, thr);
     }
-    const int ntiles = (N + 15) / 16, nkb = K / 128;
-    int ksplit = (2 * sms + ntiles - 1) / ntiles;
+    const int ntiles = (N + 63) / 64, nkb = K / 128;   // CTAs along N: four 16-column tiles each
+    int ksplit = (4 * sms + ntiles - 1) / ntiles;
     if (ksplit > nkb) ksplit = nkb;
     if (ksplit < 1) ksplit = 1;
     const int per = (nkb + ksplit - 1) / ksplit;
