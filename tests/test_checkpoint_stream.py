@@ -133,3 +133,14 @@ def test_stream_load_state_dict_on_the_gpu(tmp_path):
         la = a(idx, 16, torch.arange(6, device=dev))
         lb = b(idx, 16, torch.arange(6, device=dev))
     assert torch.equal(la, lb)
+
+
+def test_stream_load_refuses_a_cpu_model(tmp_path):
+    """The streaming loader is a CUDA pipeline (pinned staging, copy stream): a model on the CPU is refused loudly."""
+    from lit_llama.utils import stream_load_state_dict
+
+    m = torch.nn.Linear(4, 3)
+    p = tmp_path / "l.pth"
+    torch.save(m.state_dict(), p)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        stream_load_state_dict(m, p)
