@@ -11,6 +11,8 @@
 // part runs on the tensor cores (mma.sync m16n8k32 s8) with the weights as the A operand straight from
 // global memory in 16-byte loads; K is split across CTAs and combined with int32 atomics (integer addition
 // is associative: bit-deterministic).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace llb {
@@ -438,7 +440,13 @@ static int int8_linear_t(const T* x, const int8_t* cb, const int8_t* cbt, const 
       int8_act_quant_kernel<<<dim3((K + 255) / 256, Mp), 256, 0, st>>>(w.a16, w.colflag, w.sca_bits, w.ca, Mp, K, thr);
     }
     const int ntiles = (N + 63) / 64, nkb = K / 128;   // CTAs along N: four 16-column tiles each
-    int ksplit = (4 * sms + ntiles - 1) / ntiles;
+    static int mult = 0;   // CTAs aimed at, in units of the SM count (LLB200_INT8_KSPLIT_MULT, tuning)
+    if (mult == 0) {
+      const char* e = getenv("LLB200_INT8_KSPLIT_MULT");
+      mult = e ? atoi(e) : 4;
+      if (mult < 1 || mult > 16) mult = 4;
+    }
+    int ksplit = (mult * sms + ntiles - 1) / ntiles;
     if (ksplit > nkb) ksplit = nkb;
     if (ksplit < 1) ksplit = 1;
     const int per = (nkb + ksplit - 1) / ksplit;
