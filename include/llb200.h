@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define LL_ABI_VERSION 9
+#define LL_ABI_VERSION 10
 
 #define LL_OK 0
 #define LL_ERR_ARG (-1)         /* bad shape / dtype / null pointer */
@@ -162,6 +162,11 @@ typedef struct ll_gemv_args {
   uint64_t push_cnt[8];
   int32_t push_world;
   int32_t stream_kind; /* LL_STREAM_* of w / w2 (what ll_int4_prepare was asked for) */
+  /* Stream kinds 1 / 2 without the fused norm (optional): x already converted by its producer (ll_decode_attn_digits) into the
+   * kernel's own staging format - four signed base-256 digit planes [4][K + 16] bytes and [K / 128][4] float records
+   * (2^-sh, sum x, 2^(16 - sh), 0) - so that the prologue is two bulk copies.  x is then not read. */
+  const uint8_t* x_planes;
+  const float* x_rec;
 } ll_gemv_args;
 
 /* Host query: LL_OK if the GEMV takes (N, K, group, nmat, M) (LL_ERR_UNSUPPORTED otherwise, e.g. M*K too
@@ -305,6 +310,14 @@ LL_API int ll_decode_attn(const void* q, const void* k_cache, const void* v_cach
                    int B, int n_head, int head_size, int cache_len, int max_splits, float* scratch,
                    int32_t* counters, int flags, ll_stream stream);
 LL_API size_t ll_decode_attn_scratch_bytes(int B, int n_head, int head_size, int max_splits);
+/* The same attention (bf16, batch 1, head size 128, a split that fits the K/V-staging kernel: ..._supported() says so) whose
+ * per-head leader also writes y in the batch-1 GEMV's staging format: planes [4][plane_stride] bytes (plane_stride =
+ * n_head * 128 + 16), rec [n_head][4] floats - one head is one 128-element k-block of attn.c_proj's input
+ * (ll_gemv_args.x_planes / x_rec).  Same arithmetic and order as the GEMV's own conversion: identical bits downstream. */
+LL_API int ll_decode_attn_digits_supported(int dtype, int B, int head_size, int cache_len, int max_splits);
+LL_API int ll_decode_attn_digits(const void* q, const void* k_cache, const void* v_cache, const int32_t* pos, void* y, int B,
+                          int n_head, int head_size, int cache_len, int max_splits, int flags, uint8_t* planes, float* rec,
+                          int plane_stride, ll_stream stream);
 
 /* ref: MLP.forward's silu(a) * b, model.py:258, rounded like torch (silu -> dtype, product -> dtype). */
 LL_API int ll_silu_mul(const void* a, const void* b, void* y, int dtype, size_t n, ll_stream stream);

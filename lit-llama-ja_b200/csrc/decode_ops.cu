@@ -401,7 +401,8 @@ template <typename T, int HS>
 __global__ void __launch_bounds__(128) decode_attn_pf_kernel(const T* __restrict__ q, const T* __restrict__ kc,
                                                              const T* __restrict__ vc, const int32_t* __restrict__ pos,
                                                              T* __restrict__ y, int S, int nsplit, int rows_cap, int use_pdl,
-                                                             unsigned long long* __restrict__ trace) {
+                                                             unsigned long long* __restrict__ trace, uint8_t* __restrict__ dg_planes,
+                                                             float* __restrict__ dg_rec, int dg_stride) {
   ATRACE(0);
   constexpr int EPL = HS / 8, PV = piece16<T>::PV, NP = EPL / PV, PPR = HS / PV, NW = 4, RL = 6;
   static_assert(EPL % PV == 0, "a lane takes whole 16-byte pieces");
@@ -556,6 +557,7 @@ __global__ void __launch_bounds__(128) decode_attn_pf_kernel(const T* __restrict
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
   ATRACE(3);
   if (split != 0) return;
+  float outv = 0.f;
   if (threadIdx.x < HS) {
     float M = -INFINITY;
     for (int i = 0; i < nsplit; ++i) M = fmaxf(M, c_st[i][0]);
@@ -568,7 +570,56 @@ __global__ void __launch_bounds__(128) decode_attn_pf_kernel(const T* __restrict
         O += c_st[i][2 + threadIdx.x] * c;
       }
     }
-    dt<T>::st(y + (size_t)bh * HS, threadIdx.x, O / L);
+    outv = O / L;
+    dt<T>::st(y + (size_t)bh * HS, threadIdx.x, outv);
+  }
+  if constexpr (HS == 128 && sizeof(T) == 2) {
+    // One head = one 128-element k-block of attn.c_proj's input: the leader also emits the block in the form the batch-1
+    // integer-MMA GEMV stages its activations in - four signed base-256 digit planes of x * 2^sh and the block's record
+    // (2^-sh, sum x) - so that c_proj's prologue is one bulk copy instead of a conversion every CTA repeats.  Same
+    // arithmetic, in the same order, as gemv_w4a8_kernel's own staging (csrc/gemv_int4.cu): identical bits.
+    if (dg_planes != nullptr) {
+      __shared__ uint32_t s_mx[4];
+      __shared__ float s_ps[16];
+      const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+      const uint32_t xb = (uint32_t)f32_to_bf16_bits(outv);        // the value as stored
+      const float xf = bf16_bits_to_f32(xb);
+      const uint32_t mw = __reduce_max_sync(0xffffffffu, xb & 0x7fffu);
+      if (lane == 0) s_mx[warp] = mw;
+      // piece sums: 8 consecutive elements, two chains (x0 + x1 + x4 + x5) + (x2 + x3 + x6 + x7), as the GEMV's staging
+      const int l0 = lane & ~7;
+      float e[8];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) e[t] = __shfl_sync(0xffffffffu, xf, l0 + t);
+      float c0 = 0.f, c1 = 0.f;
+      c0 = __fadd_rn(c0, e[0]); c1 = __fadd_rn(c1, e[2]);
+      c0 = __fadd_rn(c0, e[1]); c1 = __fadd_rn(c1, e[3]);
+      c0 = __fadd_rn(c0, e[4]); c1 = __fadd_rn(c1, e[6]);
+      c0 = __fadd_rn(c0, e[5]); c1 = __fadd_rn(c1, e[7]);
+      if ((lane & 7) == 0) s_ps[warp * 4 + (lane >> 3)] = __fadd_rn(c0, c1);
+      __syncthreads();
+      const uint32_t mx = max(max(s_mx[0], s_mx[1]), max(s_mx[2], s_mx[3]));
+      int ex = (int)((mx >> 7) & 0xffu);
+      ex = max(ex, 32);
+      const float scale = __uint_as_float(((uint32_t)(283 - ex) << 7) << 16);   // bf16 2^(156 - ex)
+      const int vi = __float2int_rn(__fmul_rn(xf, scale));                    // exact product of two bf16 values
+      const uint32_t u = ((uint32_t)vi + 0x00808080u) ^ 0x00808080u;
+      uint8_t* dst = dg_planes + (size_t)bh * HS + threadIdx.x;
+      dst[0] = (uint8_t)(u & 0xffu);
+      dst[dg_stride] = (uint8_t)((u >> 8) & 0xffu);
+      dst[2 * (size_t)dg_stride] = (uint8_t)((u >> 16) & 0xffu);
+      dst[3 * (size_t)dg_stride] = (uint8_t)(u >> 24);
+      if (threadIdx.x == 0) {
+        float t1[8], t2[4];   // the 16-lane xor tree of the staging loop: partners 8, 4, 2, 1 apart
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t1[i] = __fadd_rn(s_ps[i], s_ps[i + 8]);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) t2[i] = __fadd_rn(t1[i], t1[i + 4]);
+        const float sum = __fadd_rn(__fadd_rn(t2[0], t2[2]), __fadd_rn(t2[1], t2[3]));
+        const float inv = __uint_as_float((uint32_t)(ex - 29) << 23);
+        *reinterpret_cast<float4*>(dg_rec + (size_t)bh * 4) = make_float4(inv, sum, inv * 65536.f, 0.f);
+      }
+    }
   }
 }
 
@@ -592,7 +643,8 @@ bool pf_ok(int cache_len, int splits) {
 // 1: launched, 0: not for this shape, < 0: error
 template <typename T, int HS>
 int launch_attn_pf(const void* q, const void* k_cache, const void* v_cache, const int32_t* pos, void* y, int cache_len,
-                   int splits, dim3 grid, dim3 block, cudaStream_t st, bool pdl, int kflags, unsigned long long* tr) {
+                   int splits, dim3 grid, dim3 block, cudaStream_t st, bool pdl, int kflags, unsigned long long* tr,
+                   uint8_t* dg_planes, float* dg_rec, int dg_stride) {
   if constexpr ((HS / 8) % piece16<T>::PV != 0) {
     return 0;
   } else {
@@ -614,7 +666,7 @@ int launch_attn_pf(const void* q, const void* k_cache, const void* v_cache, cons
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = pdl ? 2 : 1;
     LL_CUDA(cudaLaunchKernelEx(&cfg, decode_attn_pf_kernel<T, HS>, (const T*)q, (const T*)k_cache, (const T*)v_cache, pos,
-                               (T*)y, cache_len, splits, rows_cap, kflags, tr));
+                               (T*)y, cache_len, splits, rows_cap, kflags, tr, dg_planes, dg_rec, dg_stride));
     return 1;
   }
 }
@@ -737,9 +789,9 @@ __attribute__((visibility("default"))) void ll_debug_attn_trace(unsigned long lo
   g_attn_trace = buf; g_attn_trace_launches = launches; g_attn_trace_idx = 0;
 }
 
-int ll_decode_attn(const void* q, const void* k_cache, const void* v_cache, const int32_t* pos, void* y, int dtype, int B,
-                   int n_head, int head_size, int cache_len, int max_splits, float* scratch, int32_t* counters,
-                   int flags, ll_stream stream) {
+static int decode_attn_impl(const void* q, const void* k_cache, const void* v_cache, const int32_t* pos, void* y, int dtype, int B,
+                            int n_head, int head_size, int cache_len, int max_splits, float* scratch, int32_t* counters,
+                            int flags, ll_stream stream, uint8_t* dg_planes, float* dg_rec, int dg_stride) {
   LL_CHECK_ARG(q && k_cache && v_cache && pos && y, "null pointer");
   LL_CHECK_ARG(B > 0 && n_head > 0 && cache_len > 0 && max_splits >= 1 && max_splits <= 64, "bad shape");
   if (max_splits > 8) LL_CHECK_ARG(scratch && counters, "decode attention with more than 8 splits needs scratch and counters");
@@ -772,8 +824,13 @@ int ll_decode_attn(const void* q, const void* k_cache, const void* v_cache, cons
       once = true;                                                                                                \
     }                                                                                                             \
     const int pfr = cl ? launch_attn_pf<TT, HS>(q, k_cache, v_cache, pos, y, cache_len, max_splits, grid, block, st, pdl, \
-                                                kflags | (flags & (LL_ATTN_FLAG_MISGUESS | LL_ATTN_FLAG_POISON)), tr) : 0; \
+                                                kflags | (flags & (LL_ATTN_FLAG_MISGUESS | LL_ATTN_FLAG_POISON)), tr,  \
+                                                dg_planes, dg_rec, dg_stride) : 0;                                \
     if (pfr < 0) return pfr;                                                                                      \
+    if (pfr == 0 && dg_planes != nullptr) {                                                                       \
+      set_error("decode_attn_digits: this shape does not take the K/V-staging kernel");                           \
+      return LL_ERR_UNSUPPORTED;                                                                                  \
+    }                                                                                                             \
     if (pfr > 0) {                                                                                                \
     } else if (cl) {                                                                                              \
       cudaLaunchConfig_t cfg{};                                                                                   \
@@ -808,6 +865,33 @@ int ll_decode_attn(const void* q, const void* k_cache, const void* v_cache, cons
   }
 #undef ATTN
   return LL_OK;
+}
+
+int ll_decode_attn(const void* q, const void* k_cache, const void* v_cache, const int32_t* pos, void* y, int dtype, int B,
+                   int n_head, int head_size, int cache_len, int max_splits, float* scratch, int32_t* counters,
+                   int flags, ll_stream stream) {
+  return decode_attn_impl(q, k_cache, v_cache, pos, y, dtype, B, n_head, head_size, cache_len, max_splits, scratch, counters,
+                          flags, stream, nullptr, nullptr, 0);
+}
+
+int ll_decode_attn_digits_supported(int dtype, int B, int head_size, int cache_len, int max_splits) {
+  static int use_cluster = -1;
+  if (use_cluster < 0) {
+    const char* e = getenv("LLB200_ATTN_CLUSTER");
+    use_cluster = (e && atoi(e) == 0) ? 0 : 1;
+  }
+  return (dtype == LL_BF16 && B == 1 && head_size == 128 && use_cluster && max_splits >= 2 && max_splits <= 8 &&
+          pf_ok<__nv_bfloat16, 128>(cache_len, max_splits)) ? 1 : 0;
+}
+
+int ll_decode_attn_digits(const void* q, const void* k_cache, const void* v_cache, const int32_t* pos, void* y, int B, int n_head,
+                          int head_size, int cache_len, int max_splits, int flags, uint8_t* planes, float* rec, int plane_stride,
+                          ll_stream stream) {
+  LL_CHECK_ARG(planes && rec && plane_stride >= n_head * head_size && plane_stride % 16 == 0, "bad digit-plane arguments");
+  LL_CHECK_ARG(ll_decode_attn_digits_supported(LL_BF16, B, head_size, cache_len, max_splits) == 1,
+               "decode_attn_digits needs bf16, batch 1, head size 128 and a split that fits the K/V-staging kernel");
+  return decode_attn_impl(q, k_cache, v_cache, pos, y, LL_BF16, B, n_head, head_size, cache_len, max_splits, nullptr, nullptr, flags,
+                          stream, planes, rec, plane_stride);
 }
 
 int ll_silu_mul(const void* a, const void* b, void* y, int dtype, size_t n, ll_stream stream) {

@@ -80,6 +80,8 @@ struct Params {
   int off_xs, off_sx, off_red, off_wv, off_bar, off_nw;
   int prefetch_delay_ns;  // producer start delay under PDL (lets the running kernel's x staging go first)
   int helpers;            // batch-1 kernel, ODD footprint, no fused norm: the parked warps convert x too before they park
+  const uint8_t* xdg_planes;  // batch-1 kernel, no fused norm: x already as four digit planes [4][K + 16] (ll_decode_attn_digits)
+  const float* xdg_rec;       //   and per-block records [K / 128][4]: the staging is one bulk copy
   unsigned long long* trace;  // debug: [P][8] globaltimer stamps of this launch, or nullptr
 };
 
@@ -883,6 +885,7 @@ __global__ void __launch_bounds__((I8_W + 9) * 32, 1) gemv_w4a8_kernel(const __g
   const int stid = helper ? NCONS + ((int)threadIdx.x - (W + 1) * 32) : ctid;
   const int nst = helping ? (int)blockDim.x - 32 : NCONS;
   if (ctid == 0) {
+    mbar_init(&xbar[0], 1);
     mbar_init(&xbar[1], 1);
     fence_barrier_init();
     if (has_norm) {
@@ -915,169 +918,187 @@ __global__ void __launch_bounds__((I8_W + 9) * 32, 1) gemv_w4a8_kernel(const __g
   //      it); the first group stays in registers for the second pass, later groups are fetched again (an L2 hit).
   //      Arithmetic on packed bf16 pairs (HMUL2.BF16 rounds exactly where the reference's bf16 ops round) and
   //      fp32 += bf16 * bf16 (FHFMA): a fifth of the instructions of the scalar fp32 form.
-  constexpr int XR = 8;
-  constexpr uint32_t ONE2 = 0x3f803f80u;  // bf16x2 (1, 1)
-  uint4 raw[XR];
-  uint32_t rn2 = 0u;
-  const uint4* xsrc = reinterpret_cast<const uint4*>(p.x);
-  auto fetch = [&](int v0) {
-#pragma unroll
-    for (int j = 0; j < XR; ++j) {
-      const int v = v0 + j * nst + stid;
-      raw[j] = v < vpr ? __ldcg(xsrc + v) : make_uint4(0u, 0u, 0u, 0u);
-    }
-  };
-  fetch(0);
-  if (has_norm) {
-    float ss = 0.f;
-    for (int v0 = 0; v0 < vpr; v0 += XR * NCONS) {
-      uint4 r4[XR];
-      if (v0 == 0) {
-#pragma unroll
-        for (int j = 0; j < XR; ++j) r4[j] = raw[j];
-      } else {
-#pragma unroll
-        for (int j = 0; j < XR; ++j) {
-          const int v = v0 + j * NCONS + ctid;
-          r4[j] = v < vpr ? __ldcg(xsrc + v) : make_uint4(0u, 0u, 0u, 0u);
-        }
+  bool staged = false;
+  if constexpr (!has_norm) {
+    if (p.xdg_planes != nullptr) {
+      // the producer (the attention kernel's leader CTAs) already wrote x as digit planes and records in this kernel's
+      // shared-memory layout: two bulk copies instead of a conversion
+      if (ctid == 0) {
+        mbar_expect_tx(&xbar[0], (uint32_t)(4 * pstride + G * 16));
+        bulk_load_1d(xs, p.xdg_planes, (uint32_t)(4 * pstride), &xbar[0]);
+        bulk_load_1d(rec, p.xdg_rec, (uint32_t)(G * 16), &xbar[0]);
       }
-#pragma unroll
+      mbar_wait_u32(smem_u32(&xbar[0]), 0);
+      TRACE(10);
+      consumer_sync(NCONS);
+      staged = true;
+    }
+  }
+  if (!staged) {
+    constexpr int XR = 8;
+    constexpr uint32_t ONE2 = 0x3f803f80u;  // bf16x2 (1, 1)
+    uint4 raw[XR];
+    uint32_t rn2 = 0u;
+    const uint4* xsrc = reinterpret_cast<const uint4*>(p.x);
+    auto fetch = [&](int v0) {
+  #pragma unroll
       for (int j = 0; j < XR; ++j) {
-        if (v0 + j * NCONS < vpr) {  // uniform
-          const uint32_t wd[4] = {r4[j].x, r4[j].y, r4[j].z, r4[j].w};
-#pragma unroll
+        const int v = v0 + j * nst + stid;
+        raw[j] = v < vpr ? __ldcg(xsrc + v) : make_uint4(0u, 0u, 0u, 0u);
+      }
+    };
+    fetch(0);
+    if (has_norm) {
+      float ss = 0.f;
+      for (int v0 = 0; v0 < vpr; v0 += XR * NCONS) {
+        uint4 r4[XR];
+        if (v0 == 0) {
+  #pragma unroll
+          for (int j = 0; j < XR; ++j) r4[j] = raw[j];
+        } else {
+  #pragma unroll
+          for (int j = 0; j < XR; ++j) {
+            const int v = v0 + j * NCONS + ctid;
+            r4[j] = v < vpr ? __ldcg(xsrc + v) : make_uint4(0u, 0u, 0u, 0u);
+          }
+        }
+  #pragma unroll
+        for (int j = 0; j < XR; ++j) {
+          if (v0 + j * NCONS < vpr) {  // uniform
+            const uint32_t wd[4] = {r4[j].x, r4[j].y, r4[j].z, r4[j].w};
+  #pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const uint32_t sq = bf16x2_mul(wd[e], wd[e]);  // bf16(x * x), ref model.py:280
+              ss = fhfma_lo(sq, ONE2, ss);
+              ss = fhfma_hi(sq, ONE2, ss);
+            }
+          }
+        }
+      }
+      ss = warp_sum(ss);
+      if (lane == 0) s_part[warp] = ss;
+      TRACE(9);
+      consumer_sync(NCONS);
+      float tot = 0.f;
+  #pragma unroll
+      for (int w = 0; w < W; ++w) tot += s_part[w];
+      const float mean = bf16r(tot * (1.0f / (float)p.K));
+      const float rn = bf16r(rsqrtf(bf16r(mean + p.eps)));
+      rn2 = (__float_as_uint(rn) >> 16) * 0x00010001u;
+      mbar_wait_u32(smem_u32(&xbar[1]), 0);
+      TRACE(7);
+    }
+    // The conversion of one piece is a chain of dependent instructions (normalise, block maximum and sum over 16 lanes,
+    // exponent, digits, byte transposition): NP pieces of a thread go through it side by side - two with the fused norm
+    // (K = 4096: exactly the thread's two pieces), one otherwise (with helper warps most threads have a single piece).
+    constexpr int NP = has_norm ? 2 : 1;
+    for (int v0 = 0; v0 < vpr; v0 += XR * nst) {
+      if (v0 > 0) fetch(v0);
+  #pragma unroll
+      for (int j = 0; j < XR; j += NP) {
+        if (v0 + j * nst >= vpr) continue;  // uniform over the CTA
+        int v[NP];
+        bool ok[NP];
+        uint32_t wd[NP][4];
+  #pragma unroll
+        for (int q = 0; q < NP; ++q) {
+          v[q] = v0 + (j + q) * nst + stid;
+          ok[q] = v[q] < vpr;  // uniform over a half-warp: K is a multiple of 128
+          wd[q][0] = raw[j + q].x; wd[q][1] = raw[j + q].y; wd[q][2] = raw[j + q].z; wd[q][3] = raw[j + q].w;
+        }
+        if (has_norm) {  // ref model.py:276-283 rounding steps: bf16(w * bf16(x * r))
+          uint4 nraw[NP];
+  #pragma unroll
+          for (int q = 0; q < NP; ++q) {
+            nraw[q] = make_uint4(0u, 0u, 0u, 0u);
+            if (ok[q]) nraw[q] = *reinterpret_cast<const uint4*>(nws + (size_t)v[q] * 16);
+          }
+  #pragma unroll
+          for (int q = 0; q < NP; ++q) {
+            const uint32_t nw[4] = {nraw[q].x, nraw[q].y, nraw[q].z, nraw[q].w};
+  #pragma unroll
+            for (int e = 0; e < 4; ++e) wd[q][e] = bf16x2_mul(nw[e], bf16x2_mul(wd[q][e], rn2));
+          }
+        }
+        // the block's exponent from the largest magnitude of its 128 elements (16 lanes); the sum of the block for the zero term
+        uint32_t m2[NP];
+        float sum[NP];
+  #pragma unroll
+        for (int q = 0; q < NP; ++q) {
+          m2[q] = bf16x2_max(bf16x2_max(wd[q][0] & 0x7fff7fffu, wd[q][1] & 0x7fff7fffu),
+                             bf16x2_max(wd[q][2] & 0x7fff7fffu, wd[q][3] & 0x7fff7fffu));
+          float s0 = 0.f, s1 = 0.f;  // two chains
+  #pragma unroll
+          for (int e = 0; e < 4; e += 2) {
+            s0 = fhfma_lo(wd[q][e], ONE2, s0);
+            s1 = fhfma_lo(wd[q][e + 1], ONE2, s1);
+            s0 = fhfma_hi(wd[q][e], ONE2, s0);
+            s1 = fhfma_hi(wd[q][e + 1], ONE2, s1);
+          }
+          sum[q] = s0 + s1;
+        }
+  #pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {
+  #pragma unroll
+          for (int q = 0; q < NP; ++q) {
+            m2[q] = bf16x2_max(m2[q], __shfl_xor_sync(0xffffffffu, m2[q], o));
+            sum[q] += __shfl_xor_sync(0xffffffffu, sum[q], o);
+          }
+        }
+        uint32_t u[NP][8];
+        float inv[NP];
+  #pragma unroll
+        for (int q = 0; q < NP; ++q) {
+          int ex = (int)max((m2[q] >> 7) & 0xffu, (m2[q] >> 23) & 0xffu);  // biased exponent of the largest magnitude: am < 2^(ex - 126)
+          ex = max(ex, 32);                                                  // all-zero / denormal blocks: any finite scale will do
+          const uint32_t scale2 = ((uint32_t)(283 - ex) << 7) * 0x00010001u;  // bf16x2 2^(156 - ex): am * scale < 2^30
+          inv[q] = __uint_as_float((uint32_t)(ex - 29) << 23);                // 2^-(156 - ex)
+  #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            const uint32_t sq = bf16x2_mul(wd[e], wd[e]);  // bf16(x * x), ref model.py:280
-            ss = fhfma_lo(sq, ONE2, ss);
-            ss = fhfma_hi(sq, ONE2, ss);
+            const int v0i = __float2int_rn(fhfma_lo(wd[q][e], scale2, 0.f)), v1i = __float2int_rn(fhfma_hi(wd[q][e], scale2, 0.f));
+            u[q][2 * e] = ((uint32_t)v0i + 0x00808080u) ^ 0x00808080u;  // bytes = four signed base-256 digits
+            u[q][2 * e + 1] = ((uint32_t)v1i + 0x00808080u) ^ 0x00808080u;
+          }
+        }
+  #pragma unroll
+        for (int q = 0; q < NP; ++q) {
+          if (ok[q]) {
+            // 4 x 4 byte transpositions: plane d gets byte d of eight consecutive elements
+  #pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const uint32_t a = prmt(u[q][4 * h], u[q][4 * h + 1], 0x5140u), b = prmt(u[q][4 * h], u[q][4 * h + 1], 0x7362u);
+              const uint32_t cc = prmt(u[q][4 * h + 2], u[q][4 * h + 3], 0x5140u), d = prmt(u[q][4 * h + 2], u[q][4 * h + 3], 0x7362u);
+              uint8_t* dst = xs + (size_t)v[q] * 8 + h * 4;
+              *reinterpret_cast<uint32_t*>(dst) = prmt(a, cc, 0x5410u);
+              *reinterpret_cast<uint32_t*>(dst + pstride) = prmt(a, cc, 0x7632u);
+              *reinterpret_cast<uint32_t*>(dst + 2 * (size_t)pstride) = prmt(b, d, 0x5410u);
+              *reinterpret_cast<uint32_t*>(dst + 3 * (size_t)pstride) = prmt(b, d, 0x7632u);
+            }
+            if ((lane & 15) == 0) {  // record of the block: lanes tig = 0 take (inv, sum x), lanes tig = 1 take (inv * 2^16, 0)
+              float4 r;
+              r.x = inv[q];
+              r.y = sum[q];
+              r.z = inv[q] * 65536.f;
+              r.w = 0.f;
+              *reinterpret_cast<float4*>(rec + (size_t)(v[q] >> 4) * 4) = r;
+            }
           }
         }
       }
     }
-    ss = warp_sum(ss);
-    if (lane == 0) s_part[warp] = ss;
-    TRACE(9);
-    consumer_sync(NCONS);
-    float tot = 0.f;
-#pragma unroll
-    for (int w = 0; w < W; ++w) tot += s_part[w];
-    const float mean = bf16r(tot * (1.0f / (float)p.K));
-    const float rn = bf16r(rsqrtf(bf16r(mean + p.eps)));
-    rn2 = (__float_as_uint(rn) >> 16) * 0x00010001u;
-    mbar_wait_u32(smem_u32(&xbar[1]), 0);
-    TRACE(7);
-  }
-  // The conversion of one piece is a chain of dependent instructions (normalise, block maximum and sum over 16 lanes,
-  // exponent, digits, byte transposition): NP pieces of a thread go through it side by side - two with the fused norm
-  // (K = 4096: exactly the thread's two pieces), one otherwise (with helper warps most threads have a single piece).
-  constexpr int NP = has_norm ? 2 : 1;
-  for (int v0 = 0; v0 < vpr; v0 += XR * nst) {
-    if (v0 > 0) fetch(v0);
-#pragma unroll
-    for (int j = 0; j < XR; j += NP) {
-      if (v0 + j * nst >= vpr) continue;  // uniform over the CTA
-      int v[NP];
-      bool ok[NP];
-      uint32_t wd[NP][4];
-#pragma unroll
-      for (int q = 0; q < NP; ++q) {
-        v[q] = v0 + (j + q) * nst + stid;
-        ok[q] = v[q] < vpr;  // uniform over a half-warp: K is a multiple of 128
-        wd[q][0] = raw[j + q].x; wd[q][1] = raw[j + q].y; wd[q][2] = raw[j + q].z; wd[q][3] = raw[j + q].w;
+    TRACE(10);
+    if (helping) {
+      // the consumers wait for every converting thread on named barrier 3; the helper warps only arrive, then park
+      if (helper) {
+        asm volatile("bar.arrive 3, %0;" ::"r"(nst) : "memory");
+        asm volatile("bar.sync 2, %0;" ::"r"((int)blockDim.x - W * 32) : "memory");
+        return;
       }
-      if (has_norm) {  // ref model.py:276-283 rounding steps: bf16(w * bf16(x * r))
-        uint4 nraw[NP];
-#pragma unroll
-        for (int q = 0; q < NP; ++q) {
-          nraw[q] = make_uint4(0u, 0u, 0u, 0u);
-          if (ok[q]) nraw[q] = *reinterpret_cast<const uint4*>(nws + (size_t)v[q] * 16);
-        }
-#pragma unroll
-        for (int q = 0; q < NP; ++q) {
-          const uint32_t nw[4] = {nraw[q].x, nraw[q].y, nraw[q].z, nraw[q].w};
-#pragma unroll
-          for (int e = 0; e < 4; ++e) wd[q][e] = bf16x2_mul(nw[e], bf16x2_mul(wd[q][e], rn2));
-        }
-      }
-      // the block's exponent from the largest magnitude of its 128 elements (16 lanes); the sum of the block for the zero term
-      uint32_t m2[NP];
-      float sum[NP];
-#pragma unroll
-      for (int q = 0; q < NP; ++q) {
-        m2[q] = bf16x2_max(bf16x2_max(wd[q][0] & 0x7fff7fffu, wd[q][1] & 0x7fff7fffu),
-                           bf16x2_max(wd[q][2] & 0x7fff7fffu, wd[q][3] & 0x7fff7fffu));
-        float s0 = 0.f, s1 = 0.f;  // two chains
-#pragma unroll
-        for (int e = 0; e < 4; e += 2) {
-          s0 = fhfma_lo(wd[q][e], ONE2, s0);
-          s1 = fhfma_lo(wd[q][e + 1], ONE2, s1);
-          s0 = fhfma_hi(wd[q][e], ONE2, s0);
-          s1 = fhfma_hi(wd[q][e + 1], ONE2, s1);
-        }
-        sum[q] = s0 + s1;
-      }
-#pragma unroll
-      for (int o = 8; o > 0; o >>= 1) {
-#pragma unroll
-        for (int q = 0; q < NP; ++q) {
-          m2[q] = bf16x2_max(m2[q], __shfl_xor_sync(0xffffffffu, m2[q], o));
-          sum[q] += __shfl_xor_sync(0xffffffffu, sum[q], o);
-        }
-      }
-      uint32_t u[NP][8];
-      float inv[NP];
-#pragma unroll
-      for (int q = 0; q < NP; ++q) {
-        int ex = (int)max((m2[q] >> 7) & 0xffu, (m2[q] >> 23) & 0xffu);  // biased exponent of the largest magnitude: am < 2^(ex - 126)
-        ex = max(ex, 32);                                                  // all-zero / denormal blocks: any finite scale will do
-        const uint32_t scale2 = ((uint32_t)(283 - ex) << 7) * 0x00010001u;  // bf16x2 2^(156 - ex): am * scale < 2^30
-        inv[q] = __uint_as_float((uint32_t)(ex - 29) << 23);                // 2^-(156 - ex)
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int v0i = __float2int_rn(fhfma_lo(wd[q][e], scale2, 0.f)), v1i = __float2int_rn(fhfma_hi(wd[q][e], scale2, 0.f));
-          u[q][2 * e] = ((uint32_t)v0i + 0x00808080u) ^ 0x00808080u;  // bytes = four signed base-256 digits
-          u[q][2 * e + 1] = ((uint32_t)v1i + 0x00808080u) ^ 0x00808080u;
-        }
-      }
-#pragma unroll
-      for (int q = 0; q < NP; ++q) {
-        if (ok[q]) {
-          // 4 x 4 byte transpositions: plane d gets byte d of eight consecutive elements
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const uint32_t a = prmt(u[q][4 * h], u[q][4 * h + 1], 0x5140u), b = prmt(u[q][4 * h], u[q][4 * h + 1], 0x7362u);
-            const uint32_t cc = prmt(u[q][4 * h + 2], u[q][4 * h + 3], 0x5140u), d = prmt(u[q][4 * h + 2], u[q][4 * h + 3], 0x7362u);
-            uint8_t* dst = xs + (size_t)v[q] * 8 + h * 4;
-            *reinterpret_cast<uint32_t*>(dst) = prmt(a, cc, 0x5410u);
-            *reinterpret_cast<uint32_t*>(dst + pstride) = prmt(a, cc, 0x7632u);
-            *reinterpret_cast<uint32_t*>(dst + 2 * (size_t)pstride) = prmt(b, d, 0x5410u);
-            *reinterpret_cast<uint32_t*>(dst + 3 * (size_t)pstride) = prmt(b, d, 0x7632u);
-          }
-          if ((lane & 15) == 0) {  // record of the block: lanes tig = 0 take (inv, sum x), lanes tig = 1 take (inv * 2^16, 0)
-            float4 r;
-            r.x = inv[q];
-            r.y = sum[q];
-            r.z = inv[q] * 65536.f;
-            r.w = 0.f;
-            *reinterpret_cast<float4*>(rec + (size_t)(v[q] >> 4) * 4) = r;
-          }
-        }
-      }
+      asm volatile("bar.sync 3, %0;" ::"r"(nst) : "memory");
+    } else {
+      consumer_sync(NCONS);
     }
-  }
-  TRACE(10);
-  if (helping) {
-    // the consumers wait for every converting thread on named barrier 3; the helper warps only arrive, then park
-    if (helper) {
-      asm volatile("bar.arrive 3, %0;" ::"r"(nst) : "memory");
-      asm volatile("bar.sync 2, %0;" ::"r"((int)blockDim.x - W * 32) : "memory");
-      return;
-    }
-    asm volatile("bar.sync 3, %0;" ::"r"(nst) : "memory");
-  } else {
-    consumer_sync(NCONS);
-  }
+}
   TRACE(3);
 
   // epilogue operands that do not depend on this kernel's sums, fetched for this warp's first tile behind the main loop
@@ -1800,6 +1821,13 @@ int ll_int4_gemv(const ll_gemv_args* a, ll_stream stream) {
     // read per launch: the chain is captured into a graph once
     const char* e = getenv("LLB200_GEMV_HELPERS");
     p.helpers = (i8 && g_parity == LL_GEMV_ODD && a->norm_weight == nullptr && (e ? atoi(e) != 0 : true)) ? 1 : 0;
+  }
+  if (a->x_planes != nullptr) {
+    LL_CHECK_ARG(i8 && a->norm_weight == nullptr && a->x_rec != nullptr, "x_planes needs stream kind 1 / 2, no fused norm, and x_rec");
+    LL_CHECK_ARG(((uintptr_t)a->x_planes & 15) == 0 && ((uintptr_t)a->x_rec & 15) == 0, "x_planes / x_rec must be 16-byte aligned");
+    p.xdg_planes = a->x_planes;
+    p.xdg_rec = a->x_rec;
+    p.helpers = 0;
   }
   return i8 ? launch_plan_i8(p, pl, pdl, st) : launch_plan(p, pl, pdl, st);
 }

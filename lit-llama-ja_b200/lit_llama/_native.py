@@ -45,6 +45,7 @@ class GemvArgs(C.Structure):
         ("grid", C.c_int32),
         ("push_dst", C.c_uint64 * 8), ("push_cnt", C.c_uint64 * 8), ("push_world", C.c_int32),
         ("stream_kind", C.c_int32),
+        ("x_planes", vp), ("x_rec", vp),
     ]
 
 
@@ -90,6 +91,8 @@ EXPORTS = {
     "ll_rope_kv_append": ([vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp], C.c_int),
     "ll_decode_attn": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp, i32, vp], C.c_int),
     "ll_decode_attn_scratch_bytes": ([i32, i32, i32, i32], sz_t),
+    "ll_decode_attn_digits_supported": ([i32, i32, i32, i32, i32], C.c_int),
+    "ll_decode_attn_digits": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp, i32, vp], C.c_int),
     "ll_silu_mul": ([vp, vp, vp, i32, sz_t, vp], C.c_int),
     "ll_add": ([vp, vp, vp, i32, sz_t, vp], C.c_int),
     "ll_advance_pos": ([vp, i32, i32, vp], C.c_int),
@@ -98,7 +101,7 @@ EXPORTS = {
 }
 _fn = {name: _proto(name, a, r) for name, (a, r) in EXPORTS.items()}
 
-ABI_VERSION = 9
+ABI_VERSION = 10
 if _fn["ll_abi_version"]() != ABI_VERSION:
     raise ImportError("libllb200.so ABI version mismatch; rebuild with lit-llama-ja_b200/build.py")
 

@@ -117,6 +117,17 @@ class DecodeEngine:
             self.splits = int(os.environ["LLB200_ATTN_SPLITS"])
         self.attn_scratch = torch.empty(N.attn_scratch_bytes(B, nh, hs, self.splits) // 4 + 16, dtype=f32, device=dev)
         self.attn_counters = torch.zeros(B * nh, dtype=i32, device=dev)
+        # the attention kernel's per-head leader can emit attn.c_proj's input already as the GEMV's digit planes + records
+        # (one head = one 128-element k-block): c_proj's prologue is then two bulk copies instead of the conversion every
+        # CTA repeats.  Needs the K/V-staging attention kernel (bf16, batch 1, head size 128) and the integer-MMA GEMV.
+        h0p = _unwrap(h0.attn.c_proj)[0]
+        self.attn_digits = (_env_flag("LLB200_ATTN_DIGITS", True) and B == 1 and hs == 128
+                            and h0p.stream_for(B)[1] in (N.STREAM_U8, N.STREAM_W8)
+                            and N.call_ret("ll_decode_attn_digits_supported", N.LL_BF16, B, hs, max_seq_length, self.splits) == 1)
+        if self.attn_digits:
+            self.att_stride = E_loc + 16
+            self.att_planes = torch.zeros(4 * self.att_stride, dtype=torch.uint8, device=dev)
+            self.att_rec = torch.zeros(nh * 4, dtype=f32, device=dev)
         self.graph = None
         self.sample_graphs = {}                        # (temperature, top_k) -> graph of [draw, advance, step]
         self.out_tokens = torch.zeros(cfg.block_size + 2, dtype=torch.int64, device=dev)
@@ -180,6 +191,8 @@ class DecodeEngine:
             else:
                 outs, epi = self.parts, N.EPI_STORE
             a_proj = self._gemv_args(_unwrap(blk.attn.c_proj)[0], self.att, outs[0], epi, "proj")
+            if self.attn_digits:
+                a_proj.x_planes, a_proj.x_rec = self.att_planes.data_ptr(), self.att_rec.data_ptr()
             a_fc = self._gemv_args(blk.mlp.c_fc1, self.x, self.h, N.EPI_SWIGLU, "fc", norm=blk.rms_2, lin2=blk.mlp.c_fc2)
             a_down = self._gemv_args(_unwrap(blk.mlp.c_proj)[0], self.h, outs[1], epi, "down")
             if epi == N.EPI_PUSH:
@@ -202,9 +215,14 @@ class DecodeEngine:
         n = 1 if embed else 0
         for a_attn, kc, vc, a_proj, a_fc, a_down in self.layers:
             N.gemv(a_attn)
-            N.call("ll_decode_attn", N.ptr(self.q), N.ptr(kc), N.ptr(vc), N.ptr(self.pos), N.ptr(self.att), N.LL_BF16,
-                   self.B, self.nh, cfg.head_size, self.S, self.splits, N.ptr(self.attn_scratch),
-                   N.ptr(self.attn_counters), flags, st)
+            if self.attn_digits:
+                N.call("ll_decode_attn_digits", N.ptr(self.q), N.ptr(kc), N.ptr(vc), N.ptr(self.pos), N.ptr(self.att), self.B,
+                       self.nh, cfg.head_size, self.S, self.splits, flags, N.ptr(self.att_planes), N.ptr(self.att_rec),
+                       self.att_stride, st)
+            else:
+                N.call("ll_decode_attn", N.ptr(self.q), N.ptr(kc), N.ptr(vc), N.ptr(self.pos), N.ptr(self.att), N.LL_BF16,
+                       self.B, self.nh, cfg.head_size, self.S, self.splits, N.ptr(self.attn_scratch),
+                       N.ptr(self.attn_counters), flags, st)
             N.gemv(a_proj)
             if self.tp:
                 self._reduce_add(0)

@@ -185,6 +185,25 @@ def test_fused_decode_chain_at_7b_shapes_vs_oracle_and_module_path(g128, msl, n_
     assert np.array_equal(fused, again)
 
 
+def test_attention_emitted_digit_planes_give_identical_bits(g128, monkeypatch):
+    """attn.c_proj's input as digit planes written by the attention kernel's leader CTAs (ll_decode_attn_digits ->
+    ll_gemv_args.x_planes / x_rec) against the GEMV converting the bf16 row itself: the conversion is restated with the
+    same operations in the same order, so the logits must be identical bit for bit (positions through a ring wrap)."""
+    m, _ = g128
+    msl, n_prefill, n_steps = 520, PROMPT, 16
+    idx = tokens(n_prefill + n_steps, seed=77)
+    m._engine = None
+    with_digits = run_ours(m, idx, msl, n_prefill, fused=True)
+    assert m._engine is not None and m._engine.attn_digits, "the engine did not take the digit-emitting attention"
+    monkeypatch.setenv("LLB200_ATTN_DIGITS", "0")
+    m._engine = None
+    m.kv_caches.clear()
+    without = run_ours(m, idx, msl, n_prefill, fused=True)
+    assert m._engine is not None and not m._engine.attn_digits
+    m._engine = None
+    assert np.array_equal(with_digits, without)
+
+
 def test_gptq_int8_fused_decode_chain_at_7b_shapes_vs_oracle_and_module_path():
     """gptq.int8 (8-bit GPTQ weights, group 128) through the same fused decode chain: every Linear takes stream kind 2 of
     the batch-1 GEMV; against the oracle with the reference's rounding rules at 8 bits and the per-module path."""
