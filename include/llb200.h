@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define LL_ABI_VERSION 10
+#define LL_ABI_VERSION 11
 
 #define LL_OK 0
 #define LL_ERR_ARG (-1)         /* bad shape / dtype / null pointer */
@@ -301,6 +301,22 @@ LL_API int ll_rope_kv_append(const void* qkv, const float* rope, const int32_t* 
  * already selected for the T positions.  fp32 rotation of interleaved pairs, rounded to dtype. */
 LL_API int ll_apply_rope(const void* x, const float* rope, void* y, int dtype, int B, int T, int n_head, int head_size,
                   ll_stream stream);
+
+/* ref: the prefix cross-attention of LLaMA-Adapter, lit_llama/adapter.py:145-165 - the second
+ * scaled_dot_product_attention (queries against the adaption prompt's keys/values, all-true mask), the product with
+ * the per-head gating factor and the sum with the self-attention output, in one launch:
+ *   y[b][t][h][:] = dtype(y[b][t][h][:] + dtype(gate[h] * dtype(softmax(q[b][h][t] . K[h]^T / sqrt(hs)) . V[h])))
+ * q [B][nh][T][hs] (rotated, as ll_rope_kv_append leaves it); prefix_k / prefix_v [nh][prompt_len][hs] (one prompt for
+ * every batch row, prefix_batched = 0) or [B][nh][prompt_len][hs] (prefix_batched = 1, the reference's repeated
+ * layout); gate [nh]; y [B][T][nh*hs] updated in place.  head_size: multiples of 32 up to 256. */
+LL_API int ll_adapter_attn_add(const void* q, const void* prefix_k, const void* prefix_v, const void* gate, void* y,
+                               int dtype, int B, int n_head, int T, int head_size, int prompt_len, int prefix_batched,
+                               ll_stream stream);
+
+/* ref: adapter_v2_new_forward, lit_llama/adapter_v2.py:29-32, applied to a Linear's output y [rows][n]:
+ *   out = dtype(scale[c] * dtype(y[r][c] + bias[c]));  out may alias y. */
+LL_API int ll_bias_scale(const void* y, const void* bias, const void* scale, void* out, int dtype, size_t rows, int n,
+                         ll_stream stream);
 
 /* ref: F.scaled_dot_product_attention over the KV cache for ONE query token per sequence
  * (model.py:237 with T=1): attends slots [0, pos[2]).  q [B][nh][hs]; y [B][nh*hs].

@@ -94,6 +94,8 @@ EXPORTS = {
     "ll_decode_attn_digits_supported": ([i32, i32, i32, i32, i32], C.c_int),
     "ll_decode_attn_digits": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp, i32, vp], C.c_int),
     "ll_silu_mul": ([vp, vp, vp, i32, sz_t, vp], C.c_int),
+    "ll_adapter_attn_add": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp], C.c_int),
+    "ll_bias_scale": ([vp, vp, vp, vp, i32, sz_t, i32, vp], C.c_int),
     "ll_add": ([vp, vp, vp, i32, sz_t, vp], C.c_int),
     "ll_advance_pos": ([vp, i32, i32, vp], C.c_int),
     "ll_set_pos": ([vp, vp, i32, i32, vp], C.c_int),
@@ -101,7 +103,7 @@ EXPORTS = {
 }
 _fn = {name: _proto(name, a, r) for name, (a, r) in EXPORTS.items()}
 
-ABI_VERSION = 10
+ABI_VERSION = 11
 if _fn["ll_abi_version"]() != ABI_VERSION:
     raise ImportError("libllb200.so ABI version mismatch; rebuild with lit-llama-ja_b200/build.py")
 

@@ -132,6 +132,12 @@ class CausalSelfAttention(nn.Module):
         self.block_size = config.block_size
 
     def forward(self, x: torch.Tensor, step: _Step, kv_cache: Optional[KVCache] = None):
+        _, y, kv_cache = self._attend(x, step, kv_cache)
+        return self.c_proj(y), kv_cache
+
+    def _attend(self, x: torch.Tensor, step: _Step, kv_cache: Optional[KVCache] = None):
+        """Everything up to the output projection: the rotated queries ``[B, nh, T, hs]``, the attention output
+        ``[B, T, nh*hs]`` and the updated cache (the adapter model adds its prefix attention between this and c_proj)."""
         B, T, _ = x.shape
         nh, hs = self.n_head, self.head_size
         C = nh * hs                                             # width of this rank's attention output
@@ -160,7 +166,7 @@ class CausalSelfAttention(nn.Module):
             else:
                 y = F.scaled_dot_product_attention(q, k_cache, v_cache, is_causal=True, dropout_p=0.0)
             y = y.transpose(1, 2).contiguous().view(B, T, C)
-        return self.c_proj(y), kv_cache
+        return q, y, kv_cache
 
 
 class MLP(nn.Module):
@@ -208,6 +214,7 @@ class LLaMA(nn.Module):
 
     use_fused_decode = True   # single-token int4/bf16 steps go through engine.DecodeEngine
     use_step_graph = True     # other single-token steps with a KV cache (batch > 8, ...) replay one CUDA graph per (B, S)
+    graph_every_batch = False  # model families the fused engine does not take (adapter.py) graph batch 1 as well
 
     def __init__(self, config: LLaMAConfig) -> None:
         super().__init__()
@@ -279,7 +286,8 @@ class LLaMA(nn.Module):
             eng = self._fused_engine(B, max_seq_length)
             if eng is not None:
                 return eng.forward_token(idx, input_pos)
-        if (use_cache and T == 1 and self.use_step_graph and self.use_fused_decode and B > 1 and input_pos.device.type == "cuda"
+        if (use_cache and T == 1 and self.use_step_graph and ((self.use_fused_decode and B > 1) or self.graph_every_batch)
+                and input_pos.device.type == "cuda"
                 and not torch.cuda.is_current_stream_capturing() and __import__("os").environ.get("LLB200_STEP_GRAPH", "1") != "0"):
             out = self._graphed_step(idx, max_seq_length, input_pos)
             if out is not None:
@@ -341,17 +349,22 @@ class LLaMA(nn.Module):
         step = _Step(self._rope_f32, pos_ids.contiguous(), slots.contiguous(), pos3, mask, max_seq_length, use_cache)
 
         x = self.transformer.wte(idx)
-        if not use_cache:
+        if use_cache and not self.kv_caches:
+            shape = (B, self.transformer.h[0].attn.n_head, max_seq_length, self.config.head_size)
+            self.kv_caches = self._kv_from_pool(shape, x.dtype, dev)
+        x = self._run_blocks(x, step)
+        x = self.transformer.ln_f(x)
+        return self.lm_head(x)
+
+    def _run_blocks(self, x: torch.Tensor, step: _Step) -> torch.Tensor:
+        """The block loop of ref model.py:105-122 (the adapter model overrides it to carry its prefix caches along)."""
+        if not step.use_cache:
             for block in self.transformer.h:
                 x, _ = block(x, step)
         else:
-            if not self.kv_caches:
-                shape = (B, self.transformer.h[0].attn.n_head, max_seq_length, self.config.head_size)
-                self.kv_caches = self._kv_from_pool(shape, x.dtype, dev)
             for i, block in enumerate(self.transformer.h):
                 x, self.kv_caches[i] = block(x, step, self.kv_caches[i])
-        x = self.transformer.ln_f(x)
-        return self.lm_head(x)
+        return x
 
     def _kv_from_pool(self, shape, dtype, dev):
         """Zeroed KV tensors of this shape - the SAME tensors after every reset_cache(), so that captured step graphs

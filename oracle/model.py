@@ -193,8 +193,13 @@ class LLaMA:
             k, v = ck, cv
             kv = (ck, cv)
         y = sdpa(q, k, v, mask, self.dtype)
+        y = self._attn_extra(i, q, y)
         y = y.transpose(0, 2, 1, 3).reshape(B, T, C)
         return self.linears[f"transformer.h.{i}.attn.c_proj"](y, self.dtype), kv
+
+    def _attn_extra(self, i, q, y):
+        """Nothing in the plain model; oracle/adapter.py adds the prefix attention here (between SDPA and c_proj)."""
+        return y
 
     def _mlp(self, i, x):
         """MLP.forward, model.py:257-260."""
