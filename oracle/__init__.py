@@ -13,6 +13,8 @@ cites the reference file:line it follows).  Parity status:
   outputs of the unmodified reference run in the build container
   (``tests/golden/make_golden.py`` -> ``tests/golden/*.npz``); the reference's own
   test-suite holds no quantization vectors.
+* LLaMA-Adapter v1 / v2 forward (``oracle/adapter.py``): **pinned** against outputs of the
+  unmodified reference (``tests/golden/make_golden_adapter.py`` -> ``adapter_tiny.npz``).
 * llm.int8 (bitsandbytes, un-vendored and unpinned in the reference's
   requirements.txt:7): **parity unpinned** - restated from the published
   LLM.int8() algorithm (Dettmers et al., arXiv:2208.07339).
