@@ -7,7 +7,6 @@ build container (``tests/golden/make_golden_adapter.py`` -> ``tests/golden/adapt
 from __future__ import annotations
 
 from dataclasses import dataclass, field
-from typing import Optional
 
 import numpy as np
 
