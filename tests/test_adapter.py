@@ -120,6 +120,39 @@ def test_generate_adapter_surface(script, default_path):
     assert params["pretrained_path"].default == Path("checkpoints/lit-llama/7B/lit-llama.pth")
 
 
+@pytest.mark.parametrize("script", ["evaluate/adapter.py", "evaluate/adapter_v2.py"])
+def test_evaluate_adapter_surface(script):
+    """Flags of the reference's evaluate/adapter.py:50-62 (dataset names become local text files: no network)."""
+    mod = _load(script, "llb_" + script.replace("/", "_").replace(".py", ""))
+    params = inspect.signature(mod.main).parameters
+    assert list(params) == ["data_paths", "accelerator", "adapter_path", "checkpoint_path", "tokenizer_path", "dtype", "quantize"]
+    assert params["dtype"].default == "float32" and params["quantize"].default is None
+    assert "adapter_v2" in str(params["adapter_path"].default) if script.endswith("v2.py") else "out/adapter/" in str(params["adapter_path"].default)
+
+
+@pytest.mark.parametrize("v2", [False, True])
+def test_load_adapter_model_from_two_checkpoints(tmp_path, monkeypatch, v2):
+    """generate/adapter.py:57-68 (v2: generate/adapter_v2.py:64-76): the model size comes from the pretrained checkpoint's
+    embedding width, the pretrained and the adapter checkpoint are loaded one after the other through lazy_load, both
+    non-strictly; afterwards every tensor is the checkpoint's (host logic only: built on the CPU, nothing is computed)."""
+    import lit_llama.model as LM
+    import lit_llama.utils as LU
+
+    ga = _load("generate/adapter.py", "llb_generate_adapter_t")
+    W = adapter_tiny_weights(v2=v2)
+    subs = ("adapter_wte", "gating_factor", "adapter_scale", "adapter_bias")
+    torch.save({k: torch.from_numpy(v) for k, v in W.items() if not any(s in k for s in subs)}, tmp_path / "base.pth")
+    torch.save({k: torch.from_numpy(v) for k, v in W.items() if any(s in k for s in subs)}, tmp_path / "adapter.pth")
+    monkeypatch.setitem(LM.llama_configs, "adapter-tiny", dict(ADAPTER_TINY))
+    monkeypatch.setitem(LU.llama_model_sizes, ADAPTER_TINY["n_embd"], "adapter-tiny")
+    m = ga.load_adapter_model(tmp_path / "base.pth", tmp_path / "adapter.pth", None, "cpu", torch.float32, v2)
+    assert not m.training and type(m).__module__ == "lit_llama.adapter"
+    sd = m.state_dict()
+    assert set(sd) == set(W)
+    for k, v in W.items():
+        np.testing.assert_array_equal(sd[k].numpy(), v, err_msg=k)
+
+
 # ------------------------------------------------------------------------------------------ GPU: kernels
 @pytest.mark.gpu
 @pytest.mark.parametrize("dtype,hs,batched", [(torch.bfloat16, 128, 0), (torch.float32, 32, 1), (torch.bfloat16, 64, 1)])
